@@ -1,0 +1,170 @@
+/*
+ * p2p.h — C ABI of the B200 point-to-point transfer engine (libb200p2p.so).
+ *
+ * This is the drop-in boundary for the one path of AmadeusChan/test-nccl-p2p that the
+ * engine replaces: the ncclSend/ncclRecv calls of the matrix benchmark.  Every entry
+ * point below names the reference interface it stands in for (file:line into the
+ * reference's p2p_matrix.cc, or into the NCCL header that file includes).  Plain
+ * pointers, sizes and ints only; a stream is the CUDA driver's opaque `CUstream_st*`
+ * (what `cudaStream_t` already is), so the library can be bound from C, C++, ctypes, cgo…
+ *
+ * Model.  One process per GPU, one process-global engine per process (the reference has
+ * one `ncclComm_t` per process, p2p_matrix.cc:112,120).  All ranks live on one host and
+ * reach each other over NVLink/NVSwitch.  Bootstrap is two-phase so any transport can
+ * carry it (MPI_Allgather in include/p2p_mpi.h, torch.distributed in the Python binding):
+ *
+ *     p2p_init(rank, nranks, device);
+ *     p2p_export(my_blob);      // p2p_blob_bytes() bytes
+ *     <allgather the blobs in rank order>
+ *     p2p_connect(all_blobs);
+ *
+ * Receive buffers of messages larger than the eager limit must lie inside a registered
+ * window (p2p_register_export / p2p_register_import, same two-phase shape), because the
+ * sender's kernel stores straight into them through a peer mapping: one NVLink crossing,
+ * no staging copy.  Send buffers need no registration.
+ *
+ * Matching rules are NCCL's (nccl.h:438-462): the k-th p2p_send(count, dtype, peer=B) on
+ * rank A pairs with the k-th p2p_recv(count, dtype, peer=A) on rank B, byte counts must
+ * agree, calls return after enqueue and complete in stream order, and a send and a recv
+ * that must make progress together (bidirectional exchange, self-send) belong in one
+ * p2p_group_start()/p2p_group_end() pair.
+ */
+#ifndef B200_P2P_H
+#define B200_P2P_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define P2P_API __attribute__((visibility("default")))
+#else
+#define P2P_API
+#endif
+
+/* Same opaque type cuda_runtime.h calls cudaStream_t. */
+struct CUstream_st;
+typedef struct CUstream_st* p2p_stream_t;
+
+/* Result codes: numeric values follow ncclResult_t (nccl.h:41-49) so that code which
+ * tests `!= ncclSuccess` keeps working.  The reference wraps calls in NCCLCHECK
+ * (p2p_matrix.cc:35-42); P2PCHECK in include/p2p_mpi.h is the same macro. */
+typedef enum {
+    P2P_SUCCESS = 0,
+    P2P_UNHANDLED_CUDA_ERROR = 1,
+    P2P_SYSTEM_ERROR = 2,
+    P2P_INTERNAL_ERROR = 3,
+    P2P_INVALID_ARGUMENT = 4,
+    P2P_INVALID_USAGE = 5,
+    P2P_REMOTE_ERROR = 6, /* a peer did not answer within the timeout */
+    P2P_IN_PROGRESS = 7,
+    P2P_NUM_RESULTS = 8
+} p2p_result_t;
+
+/* Element types: numeric values are ncclDataType_t's (nccl.h:278-291), so the reference's
+ * `ncclInt8` argument (p2p_matrix.cc:158) can be passed through unchanged.  The type only
+ * scales `count` to bytes; payloads are opaque. */
+typedef enum {
+    P2P_INT8 = 0, P2P_CHAR = 0,
+    P2P_UINT8 = 1,
+    P2P_INT32 = 2, P2P_INT = 2,
+    P2P_UINT32 = 3,
+    P2P_INT64 = 4,
+    P2P_UINT64 = 5,
+    P2P_FLOAT16 = 6, P2P_HALF = 6,
+    P2P_FLOAT32 = 7, P2P_FLOAT = 7,
+    P2P_FLOAT64 = 8, P2P_DOUBLE = 8,
+    P2P_BFLOAT16 = 9,
+    P2P_FLOAT8E4M3 = 10,
+    P2P_FLOAT8E5M2 = 11,
+    P2P_NUM_TYPES = 12
+} p2p_datatype_t;
+
+#define P2P_MAX_RANKS 16      /* one NVSwitch domain on one host */
+#define P2P_MAX_WINDOWS 256   /* registered windows per rank */
+#define P2P_MAX_GROUP_OPS 32  /* sends + recvs in one group */
+
+/* ---- lifecycle: replaces ncclGetUniqueId + MPI_Bcast + ncclCommInitRank
+ *      (p2p_matrix.cc:115-120) and ncclCommDestroy (p2p_matrix.cc:270) ---- */
+
+/* Create this process's engine on CUDA device `device` (the reference's
+ * `rank % gpus_per_host`, p2p_matrix.cc:99,119).  Makes that device current. */
+P2P_API int p2p_init(int rank, int nranks, int device);
+/* Size of one rank's bootstrap blob (constant for a given library build). */
+P2P_API size_t p2p_blob_bytes(void);
+/* Fill `blob` with this rank's control-region handle and identity. */
+P2P_API int p2p_export(void* blob);
+/* `all_blobs` holds nranks blobs in rank order.  Maps every peer's control region and
+ * enables peer access.  Fails with P2P_INVALID_USAGE if ranks span several hosts (NVLink
+ * peer mappings do not cross hosts; the reference tolerates it, p2p_matrix.cc:78-99). */
+P2P_API int p2p_connect(const void* all_blobs);
+/* Drain, unmap peers, free engine memory.  User buffers are never freed by the library. */
+P2P_API int p2p_finalize(void);
+P2P_API int p2p_rank(void);
+P2P_API int p2p_nranks(void);
+
+/* ---- windows: stand in for ncclCommWindowRegister / ncclCommRegister
+ *      (nccl.h:243,251); the reference's buffers are plain cudaMalloc (p2p_matrix.cc:127-128),
+ *      which is exactly what this accepts ---- */
+
+/* Collective, two-phase like bootstrap.  `buf` may be NULL with bytes == 0 on ranks that
+ * contribute nothing.  `buf` must come from cudaMalloc (any offset inside an allocation). */
+P2P_API size_t p2p_register_blob_bytes(void);   /* 128 */
+P2P_API int p2p_register_export(void* buf, size_t bytes, void* blob);
+P2P_API int p2p_register_import(const void* all_blobs, int* window_id);
+/* Collective by convention: every rank drops the same window. */
+P2P_API int p2p_deregister(int window_id);
+/* Convenience for bindings that cannot call cudaMalloc themselves (ctypes, cgo). */
+P2P_API int p2p_mem_alloc(void** ptr, size_t bytes);   /* nccl.h:130 ncclMemAlloc */
+P2P_API int p2p_mem_free(void* ptr);                   /* nccl.h:140 ncclMemFree */
+
+/* ---- the hot path: replaces ncclSend / ncclRecv (nccl.h:442,461; call sites
+ *      p2p_matrix.cc:157-161, 165-169, 215-225, 236-246) ---- */
+
+P2P_API int p2p_send(const void* buf, size_t count, int dtype, int peer, p2p_stream_t stream);
+P2P_API int p2p_recv(void* buf, size_t count, int dtype, int peer, p2p_stream_t stream);
+/* replace ncclGroupStart / ncclGroupEnd (nccl.h:493,503; p2p_matrix.cc:212,227,233,248).
+ * All operations of a group run as ONE kernel launched on the stream of the group's first
+ * operation; the other streams named in the group wait for it and it waits for them. */
+P2P_API int p2p_group_start(void);
+P2P_API int p2p_group_end(void);
+
+/* ---- errors: ncclGetErrorString / ncclGetLastError / ncclCommGetAsyncError
+ *      (nccl.h:215,219,227) ---- */
+P2P_API const char* p2p_get_error_string(int result);
+P2P_API const char* p2p_get_last_error(void);
+/* Non-blocking: P2P_SUCCESS, or the first error a device kernel reported (peer timeout). */
+P2P_API int p2p_get_async_error(int* result);
+
+/* ---- tuning knobs (the reference has none; NCCL reads NCCL_* environment variables).
+ *      Names: "path" (0 auto, 1 ldst, 2 tma, 3 ce), "nblocks" (CTAs per send, 0 auto),
+ *      "eager_bytes" (LL limit; must match on all ranks, set before p2p_export),
+ *      "timeout_ms" (device spin timeout), "unroll". Environment: P2P_PATH, P2P_NBLOCKS,
+ *      P2P_EAGER_BYTES, P2P_TIMEOUT_MS read once in p2p_init. ---- */
+P2P_API int p2p_set_option(const char* name, long long value);
+P2P_API int p2p_get_option(const char* name, long long* value);
+/* What the selector would do for a message of `bytes` to `peer`: writes the path id
+ * (1 ldst, 2 tma, 3 ce, 4 eager) and CTA count. */
+P2P_API int p2p_query_plan(size_t bytes, int peer, int* path, int* nblocks);
+
+/* ---- verification support: the reference sends zeros and never reads recv_buff
+ *      (p2p_matrix.cc:129-130); parity needs a pattern.  Byte i of (seed, rank, iter) is
+ *      byte (i & 7) of splitmix64(seed ^ rank<<48 ^ iter<<24 … ) — see oracle/pattern.h for
+ *      the CPU restatement these kernels are tested against. ---- */
+P2P_API int p2p_pattern_fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter,
+                             p2p_stream_t stream);
+/* Counts bytes of `buf` that differ from the pattern; synchronises `stream`.  Also returns
+ * the offset of the first mismatch (or bytes if none) and a 64-bit digest of the buffer. */
+P2P_API int p2p_pattern_check(const void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter,
+                              p2p_stream_t stream, uint64_t* mismatches, uint64_t* first_bad,
+                              uint64_t* digest);
+/* 64-bit order-dependent digest of any device buffer (same function as above). */
+P2P_API int p2p_digest(const void* buf, size_t bytes, p2p_stream_t stream, uint64_t* digest);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_P2P_H */

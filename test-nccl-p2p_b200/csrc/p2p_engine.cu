@@ -1,0 +1,891 @@
+// Host side of the transfer engine: bootstrap, window registration, the group builder that
+// turns p2p_send/p2p_recv calls into one fused kernel launch, plan selection, error reporting.
+// C ABI in include/p2p.h; reference call sites it stands in for are cited there.
+#include "p2p.h"
+#include "p2p_internal.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+#include <unistd.h>
+
+namespace p2p {
+namespace {
+
+constexpr uint32_t kBlobMagic = 0x42325032u;  // "B2P2"
+constexpr uint32_t kBlobVersion = 1;
+constexpr size_t kBlobBytes = 256;
+constexpr size_t kRegBlobBytes = 128;
+
+struct BootBlob {
+    uint32_t magic, version;
+    int32_t rank, nranks;
+    uint64_t host_hash;
+    int32_t pid, device;
+    uint64_t eager_bytes;
+    uint64_t ctl_bytes;
+    char pci_bus_id[32];
+    cudaIpcMemHandle_t ctl_handle;
+};
+static_assert(sizeof(BootBlob) <= kBlobBytes, "bootstrap blob too large");
+
+struct RegBlob {
+    uint32_t magic;
+    int32_t has;
+    uint64_t bytes;
+    uint64_t offset;  // of the window inside its cudaMalloc allocation
+    cudaIpcMemHandle_t handle;
+};
+static_assert(sizeof(RegBlob) <= kRegBlobBytes, "register blob too large");
+
+// Section of a rank's control region that belongs to one peer.  Who writes what:
+//   post[]   the peer, as receiver of my sends   (I poll it as sender)
+//   done[]   the peer, as sender to me           (I poll it as receiver)
+//   ll_ack[] the peer, as eager receiver         (I poll it as eager sender)
+struct PeerCtl {
+    uint64_t post[kRing];
+    uint64_t done[kRing];
+    uint64_t ll_ack[kLLSlots];
+    uint64_t pad[8];
+};
+
+struct Window {
+    bool used = false;
+    uint8_t* base = nullptr;  // local buffer (may be null if this rank contributed nothing)
+    size_t bytes = 0;
+    uint8_t* peer_base[P2P_MAX_RANKS] = {};  // mapped address of every rank's part of this window
+    std::string peer_handle[P2P_MAX_RANKS];  // key into ipc_cache for unmapping
+};
+
+struct IpcMapping {
+    void* ptr = nullptr;
+    int refs = 0;
+};
+
+struct PendingOp {
+    bool is_send;
+    const void* buf;
+    size_t nbytes;
+    int peer;
+    cudaStream_t stream;
+};
+
+struct Options {
+    long long path = 0;        // 0 auto, 1 ldst, 2 tma, 3 ce
+    long long nblocks = 0;     // CTAs per send to a peer, 0 auto
+    long long self_nblocks = 0;
+    long long eager_bytes = 16 * 1024;
+    long long timeout_ms = 20000;
+    long long vec_bytes = 16;
+    long long tma_chunk = 16 * 1024;
+    long long tma_stages = 8;
+    long long tma_min_bytes = -1;  // auto: sizes at or above this use the TMA flavour (-1 never)
+};
+
+struct Engine {
+    bool inited = false, connected = false;
+    int rank = -1, nranks = 0, device = -1, sm_count = 0;
+    int ctas_ldst = 2, ctas_tma = 1;
+    uint64_t host_hash = 0;
+    Options opt;
+
+    size_t ctl_bytes = 0, ll_slot_bytes = 0, ll_off = 0;
+    uint8_t* ctl = nullptr;                     // my control region (exported)
+    uint8_t* peer_ctl[P2P_MAX_RANKS] = {};      // everyone's, peer-mapped (mine == ctl)
+    uint32_t* arrive = nullptr;                 // [nranks][kRing] local arrival counters
+    uint64_t* win_table = nullptr;              // [nranks][P2P_MAX_WINDOWS] device table of mapped bases
+    CheckPartial* chk_partials = nullptr;       // scratch for pattern_check
+    unsigned int* chk_ticket = nullptr;
+    CheckPartial* chk_out = nullptr;
+    CheckPartial* chk_out_host = nullptr;       // pinned
+    uint32_t* async_err_host = nullptr;         // pinned + mapped
+    uint32_t* async_err_dev = nullptr;
+
+    uint64_t rdv_send_seq[P2P_MAX_RANKS] = {}, rdv_recv_seq[P2P_MAX_RANKS] = {};
+    uint64_t ll_send_seq[P2P_MAX_RANKS] = {}, ll_recv_seq[P2P_MAX_RANKS] = {};
+
+    Window windows[P2P_MAX_WINDOWS];
+    std::map<std::string, IpcMapping> ipc_cache[P2P_MAX_RANKS];
+    void* pending_reg_buf = nullptr;
+    size_t pending_reg_bytes = 0;
+    bool has_pending_reg = false;
+
+    int group_depth = 0;
+    std::vector<PendingOp> group_ops;
+    cudaEvent_t ev_done = nullptr;
+    std::vector<cudaEvent_t> ev_pool;
+
+    std::mutex mu;
+};
+
+Engine g;
+thread_local char t_last_error[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_last_error, sizeof t_last_error, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t e_ = (expr);                                                                \
+        if (e_ != cudaSuccess)                                                                  \
+            return fail(P2P_UNHANDLED_CUDA_ERROR, "%s failed: %s (%s:%d)", #expr,               \
+                        cudaGetErrorString(e_), __FILE__, __LINE__);                            \
+    } while (0)
+
+// DJB2a over the short host name, as the reference does (p2p_matrix.cc:44-61).
+uint64_t host_hash_now() {
+    char name[1024];
+    if (gethostname(name, sizeof name) != 0) name[0] = '\0';
+    name[sizeof name - 1] = '\0';
+    uint64_t h = 5381;
+    for (int i = 0; name[i] != '\0' && name[i] != '.'; ++i) h = ((h << 5) + h) ^ (uint64_t)name[i];
+    return h;
+}
+
+const size_t kDtypeSize[P2P_NUM_TYPES] = {1, 1, 4, 4, 8, 8, 2, 4, 8, 2, 1, 1};
+
+inline PeerCtl* peer_section(uint8_t* region, int p) { return (PeerCtl*)region + p; }
+inline uint8_t* ll_slot(uint8_t* region, int from, uint64_t seq) {
+    return region + g.ll_off + ((size_t)from * kLLSlots + (size_t)(seq % kLLSlots)) * g.ll_slot_bytes;
+}
+
+long long env_ll(const char* name, long long dflt) {
+    const char* s = getenv(name);
+    if (!s || !*s) return dflt;
+    if (!strcmp(name, "P2P_PATH")) {
+        if (!strcmp(s, "auto")) return 0;
+        if (!strcmp(s, "ldst")) return 1;
+        if (!strcmp(s, "tma")) return 2;
+        if (!strcmp(s, "ce")) return 3;
+    }
+    char* end = nullptr;
+    long long v = strtoll(s, &end, 0);
+    return end == s ? dflt : v;
+}
+
+int check_ready() {
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (!g.connected) return fail(P2P_INVALID_USAGE, "p2p_connect has not been called");
+    return P2P_SUCCESS;
+}
+
+// ---- plan selection -----------------------------------------------------------------
+
+struct Plan {
+    int path;      // 1 ldst, 2 tma, 4 eager
+    int nblocks;
+};
+
+Plan plan_for(size_t nbytes, int peer) {
+    Plan p{};
+    if ((long long)nbytes <= g.opt.eager_bytes) {
+        p.path = 4;
+        p.nblocks = 1;
+        return p;
+    }
+    const bool self = (peer == g.rank);
+    int path = (int)g.opt.path;
+    if (path == 0 || path == 3)
+        path = (g.opt.tma_min_bytes >= 0 && (long long)nbytes >= g.opt.tma_min_bytes) ? 2 : 1;
+    p.path = path;
+    if (path == 2) {
+        const size_t chunks = (nbytes + (size_t)g.opt.tma_chunk - 1) / (size_t)g.opt.tma_chunk;
+        long long cap = self ? (g.opt.self_nblocks ? g.opt.self_nblocks : g.sm_count * g.ctas_tma)
+                             : (g.opt.nblocks ? g.opt.nblocks : 32);
+        // keep every CTA's ring busy: at least two chunks each
+        p.nblocks = (int)std::max<size_t>(1, std::min<size_t>((chunks + 1) / 2, (size_t)cap));
+    } else {
+        const size_t tile = (size_t)kLdstThreads * 128;  // bytes one CTA moves per loop trip
+        const size_t tiles = (nbytes + tile - 1) / tile;
+        long long cap = self ? (g.opt.self_nblocks ? g.opt.self_nblocks : g.sm_count * g.ctas_ldst)
+                             : (g.opt.nblocks ? g.opt.nblocks : 32);
+        p.nblocks = (int)std::max<size_t>(1, std::min<size_t>(tiles, (size_t)cap));
+    }
+    return p;
+}
+
+int find_window(const void* buf, size_t nbytes, uint32_t* win, uint64_t* off) {
+    const uint8_t* b = (const uint8_t*)buf;
+    for (int w = 0; w < P2P_MAX_WINDOWS; ++w) {
+        const Window& W = g.windows[w];
+        if (!W.used || !W.base) continue;
+        if (b >= W.base && b + nbytes <= W.base + W.bytes) {
+            *win = (uint32_t)w;
+            *off = (uint64_t)(b - W.base);
+            return P2P_SUCCESS;
+        }
+    }
+    return fail(P2P_INVALID_USAGE,
+                "p2p_recv: buffer %p (+%zu bytes) is not inside a registered window; messages larger than "
+                "the eager limit (%lld bytes) are stored directly into the receive buffer by the sender and "
+                "need p2p_register_export/import first",
+                buf, nbytes, g.opt.eager_bytes);
+}
+
+// ---- group launch --------------------------------------------------------------------
+
+int launch_pending() {
+    std::vector<PendingOp> ops;
+    ops.swap(g.group_ops);
+    if (ops.empty()) return P2P_SUCCESS;
+    if (ops.size() > (size_t)kMaxGroupOps)
+        return fail(P2P_INVALID_USAGE, "a group holds at most %d operations (got %zu)", kMaxGroupOps, ops.size());
+
+    // validate everything before any sequence number moves
+    struct Resolved { Plan plan; uint32_t win; uint64_t off; };
+    std::vector<Resolved> res(ops.size());
+    int flavour = FLAVOUR_LDST;
+    for (size_t i = 0; i < ops.size(); ++i) {
+        const PendingOp& op = ops[i];
+        res[i].plan = plan_for(op.nbytes, op.peer);
+        res[i].win = 0;
+        res[i].off = 0;
+        if (res[i].plan.path != 4 && !op.is_send) {
+            int rc = find_window(op.buf, op.nbytes, &res[i].win, &res[i].off);
+            if (rc) return rc;
+        }
+        if (res[i].plan.path == 2 && op.is_send) flavour = FLAVOUR_TMA;
+    }
+    if (flavour == FLAVOUR_TMA) {
+        // one flavour per launch: re-plan ld/st sends of this group for the TMA kernel
+        const long long keep = g.opt.path;
+        g.opt.path = 2;
+        for (size_t i = 0; i < ops.size(); ++i)
+            if (ops[i].is_send && res[i].plan.path == 1) res[i].plan = plan_for(ops[i].nbytes, ops[i].peer);
+        g.opt.path = keep;
+    }
+
+    GroupArgs args;
+    memset(&args, 0, sizeof args);
+    args.vec_bytes = (uint32_t)g.opt.vec_bytes;
+    args.tma_chunk = (uint32_t)g.opt.tma_chunk;
+    args.tma_stages = (uint32_t)g.opt.tma_stages;
+    args.timeout_ns = (uint64_t)g.opt.timeout_ms * 1000000ull;
+    args.async_err = g.async_err_dev;
+
+    // CTA budget: everything should be co-resident so that no role waits for an SM
+    const int per_sm = flavour == FLAVOUR_TMA ? g.ctas_tma : g.ctas_ldst;
+    long long budget = (long long)g.sm_count * per_sm;
+    uint32_t n_ctrl = 0, n_fixed = 0;
+    long long want_send = 0;
+    for (size_t i = 0; i < ops.size(); ++i) {
+        if (res[i].plan.path == 4) ++n_fixed;
+        else if (!ops[i].is_send) ++n_ctrl;
+        else want_send += res[i].plan.nblocks;
+    }
+    budget -= n_fixed + (n_ctrl ? 1 : 0);
+    if (budget < 1) budget = 1;
+    if (want_send > budget) {
+        for (size_t i = 0; i < ops.size(); ++i)
+            if (ops[i].is_send && res[i].plan.path != 4)
+                res[i].plan.nblocks = (int)std::max<long long>(1, res[i].plan.nblocks * budget / want_send);
+    }
+
+    uint32_t next_block = n_ctrl ? 1 : 0;
+    args.n_ctrl = n_ctrl;
+    uint8_t* my = g.ctl;
+    const int me = g.rank;
+    // order: eager receives, eager sends, then the rendezvous pushes (control CTA is block 0)
+    for (int pass = 0; pass < 4; ++pass) {
+        for (size_t i = 0; i < ops.size(); ++i) {
+            const PendingOp& op = ops[i];
+            const bool eager = res[i].plan.path == 4;
+            const int cls = !op.is_send ? (eager ? 1 : 0) : (eager ? 2 : 3);
+            if (cls != pass) continue;
+            OpDesc& d = args.ops[args.nops++];
+            const int p = op.peer;
+            uint8_t* theirs = g.peer_ctl[p];
+            d.local = (uint64_t)op.buf;
+            d.nbytes = op.nbytes;
+            d.peer = (uint32_t)p;
+            if (cls == 0) {  // rendezvous receive
+                const uint64_t seq = ++g.rdv_recv_seq[p];
+                d.kind = OP_RECV_RDV;
+                d.seq = seq;
+                d.word = make_post_word(seq, res[i].win, res[i].off);
+                d.signal_flag = (uint64_t)&peer_section(theirs, me)->post[seq % kRing];
+                d.wait_flag = (uint64_t)&peer_section(my, p)->done[seq % kRing];
+            } else if (cls == 1) {  // eager receive
+                const uint64_t seq = ++g.ll_recv_seq[p];
+                d.kind = OP_RECV_LL;
+                d.seq = seq;
+                d.aux = (uint64_t)ll_slot(my, p, seq);
+                d.signal_flag = (uint64_t)&peer_section(theirs, me)->ll_ack[seq % kLLSlots];
+                d.first_block = next_block;
+                d.nblocks = 1;
+                next_block += 1;
+            } else if (cls == 2) {  // eager send
+                const uint64_t seq = ++g.ll_send_seq[p];
+                d.kind = OP_SEND_LL;
+                d.seq = seq;
+                d.aux = (uint64_t)ll_slot(theirs, me, seq);
+                d.wait_flag = (uint64_t)&peer_section(my, p)->ll_ack[seq % kLLSlots];
+                d.first_block = next_block;
+                d.nblocks = 1;
+                next_block += 1;
+            } else {  // rendezvous send
+                const uint64_t seq = ++g.rdv_send_seq[p];
+                d.kind = OP_SEND_RDV;
+                d.seq = seq;
+                d.wait_flag = (uint64_t)&peer_section(my, p)->post[seq % kRing];
+                d.signal_flag = (uint64_t)&peer_section(theirs, me)->done[seq % kRing];
+                d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
+                d.arrive = (uint64_t)(g.arrive + (size_t)p * kRing + seq % kRing);
+                d.first_block = next_block;
+                d.nblocks = (uint32_t)res[i].plan.nblocks;
+                next_block += d.nblocks;
+            }
+        }
+    }
+    const uint32_t grid = next_block;
+    if (grid == 0) return P2P_SUCCESS;
+
+    // streams: launch on the first op's stream; the others wait for the kernel and it for them
+    cudaStream_t launch_stream = ops[0].stream;
+    std::vector<cudaStream_t> others;
+    for (const PendingOp& op : ops)
+        if (op.stream != launch_stream && std::find(others.begin(), others.end(), op.stream) == others.end())
+            others.push_back(op.stream);
+    while (g.ev_pool.size() < others.size()) {
+        cudaEvent_t e;
+        CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        g.ev_pool.push_back(e);
+    }
+    for (size_t i = 0; i < others.size(); ++i) {
+        CUDA_TRY(cudaEventRecord(g.ev_pool[i], others[i]));
+        CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ev_pool[i], 0));
+    }
+    const int dyn_smem = flavour == FLAVOUR_TMA ? (int)(g.opt.tma_chunk * g.opt.tma_stages) : 0;
+    CUDA_TRY(launch_group(flavour, args, grid, dyn_smem, launch_stream));
+    if (!others.empty()) {
+        CUDA_TRY(cudaEventRecord(g.ev_done, launch_stream));
+        for (cudaStream_t s : others) CUDA_TRY(cudaStreamWaitEvent(s, g.ev_done, 0));
+    }
+    return P2P_SUCCESS;
+}
+
+int enqueue(bool is_send, const void* buf, size_t count, int dtype, int peer, cudaStream_t stream) {
+    int rc = check_ready();
+    if (rc) return rc;
+    if (dtype < 0 || dtype >= P2P_NUM_TYPES) return fail(P2P_INVALID_ARGUMENT, "unknown datatype %d", dtype);
+    if (peer < 0 || peer >= g.nranks) return fail(P2P_INVALID_ARGUMENT, "peer %d out of range [0,%d)", peer, g.nranks);
+    const size_t es = kDtypeSize[dtype];
+    if (count > (SIZE_MAX / es)) return fail(P2P_INVALID_ARGUMENT, "count %zu overflows size_t", count);
+    const size_t nbytes = count * es;
+    if (nbytes > kPostOffMask) return fail(P2P_INVALID_ARGUMENT, "message of %zu bytes exceeds the 512 GiB limit", nbytes);
+    if (nbytes && !buf) return fail(P2P_INVALID_ARGUMENT, "null buffer with count %zu", count);
+    std::lock_guard<std::mutex> lk(g.mu);
+    g.group_ops.push_back(PendingOp{is_send, buf, nbytes, peer, stream});
+    if (g.group_depth == 0) return launch_pending();
+    return P2P_SUCCESS;
+}
+
+void* ipc_open(int peer, const cudaIpcMemHandle_t& h, std::string* key_out, cudaError_t* err) {
+    std::string key((const char*)&h, sizeof h);
+    auto& cache = g.ipc_cache[peer];
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+        it->second.refs++;
+        *key_out = key;
+        *err = cudaSuccess;
+        return it->second.ptr;
+    }
+    void* ptr = nullptr;
+    *err = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (*err != cudaSuccess) return nullptr;
+    cache[key] = IpcMapping{ptr, 1};
+    *key_out = key;
+    return ptr;
+}
+
+void ipc_close(int peer, const std::string& key) {
+    auto& cache = g.ipc_cache[peer];
+    auto it = cache.find(key);
+    if (it == cache.end()) return;
+    if (--it->second.refs == 0) {
+        cudaIpcCloseMemHandle(it->second.ptr);
+        cache.erase(it);
+    }
+}
+
+typedef int (*cuMemGetAddressRange_t)(unsigned long long* pbase, size_t* psize, unsigned long long dptr);
+
+int allocation_range(void* ptr, uint8_t** base, size_t* size) {
+    static cuMemGetAddressRange_t fn = nullptr;
+    if (!fn) {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuMemGetAddressRange", &sym, cudaEnableDefault, &q);
+        if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !sym)
+            return fail(P2P_SYSTEM_ERROR, "cannot resolve cuMemGetAddressRange from the driver");
+        fn = (cuMemGetAddressRange_t)sym;
+    }
+    unsigned long long b = 0;
+    size_t s = 0;
+    int r = fn(&b, &s, (unsigned long long)ptr);
+    if (r != 0) return fail(P2P_INVALID_ARGUMENT, "%p is not device memory known to the driver (cuMemGetAddressRange=%d)", ptr, r);
+    *base = (uint8_t*)b;
+    *size = s;
+    return P2P_SUCCESS;
+}
+
+}  // namespace
+}  // namespace p2p
+
+using namespace p2p;
+
+// ======================================================================== C ABI
+
+extern "C" {
+
+int p2p_init(int rank, int nranks, int device) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (g.inited) return fail(P2P_INVALID_USAGE, "p2p_init called twice");
+    if (nranks < 1 || nranks > P2P_MAX_RANKS)
+        return fail(P2P_INVALID_ARGUMENT, "nranks %d outside [1,%d]", nranks, P2P_MAX_RANKS);
+    if (rank < 0 || rank >= nranks) return fail(P2P_INVALID_ARGUMENT, "rank %d outside [0,%d)", rank, nranks);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(P2P_UNHANDLED_CUDA_ERROR, "no CUDA device available (%s); this engine has no CPU path",
+                    cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(P2P_INVALID_ARGUMENT, "device %d outside [0,%d)", device, ndev);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(P2P_INVALID_USAGE, "device %d is sm_%d%d; this library contains sm_100a code only", device,
+                    prop.major, prop.minor);
+    g.rank = rank;
+    g.nranks = nranks;
+    g.device = device;
+    g.sm_count = prop.multiProcessorCount;
+    g.host_hash = host_hash_now();
+
+    Options& o = g.opt;
+    o = Options();
+    o.path = env_ll("P2P_PATH", o.path);
+    o.nblocks = env_ll("P2P_NBLOCKS", o.nblocks);
+    o.self_nblocks = env_ll("P2P_SELF_NBLOCKS", o.self_nblocks);
+    o.eager_bytes = env_ll("P2P_EAGER_BYTES", o.eager_bytes);
+    o.timeout_ms = env_ll("P2P_TIMEOUT_MS", o.timeout_ms);
+    o.vec_bytes = env_ll("P2P_VEC_BYTES", o.vec_bytes);
+    o.tma_chunk = env_ll("P2P_TMA_CHUNK", o.tma_chunk);
+    o.tma_stages = env_ll("P2P_TMA_STAGES", o.tma_stages);
+    o.tma_min_bytes = env_ll("P2P_TMA_MIN_BYTES", o.tma_min_bytes);
+    if (o.eager_bytes < 0 || o.eager_bytes > (1 << 20))
+        return fail(P2P_INVALID_ARGUMENT, "P2P_EAGER_BYTES %lld outside [0, 1 MiB]", o.eager_bytes);
+
+    // control region: per-peer flag sections, then the eager rings
+    g.ll_slot_bytes = (size_t)std::max<long long>(o.eager_bytes, 8) * 2;
+    g.ll_slot_bytes = (g.ll_slot_bytes + 255) & ~(size_t)255;
+    g.ll_off = (sizeof(PeerCtl) * (size_t)nranks + 4095) & ~(size_t)4095;
+    g.ctl_bytes = g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes;
+    CUDA_TRY(cudaMalloc(&g.ctl, g.ctl_bytes));
+    CUDA_TRY(cudaMemset(g.ctl, 0, g.ctl_bytes));
+    CUDA_TRY(cudaMalloc(&g.arrive, sizeof(uint32_t) * (size_t)nranks * kRing));
+    CUDA_TRY(cudaMemset(g.arrive, 0, sizeof(uint32_t) * (size_t)nranks * kRing));
+    CUDA_TRY(cudaMalloc(&g.win_table, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
+    CUDA_TRY(cudaMemset(g.win_table, 0, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
+    CUDA_TRY(cudaMalloc(&g.chk_partials, sizeof(CheckPartial) * (size_t)g.sm_count * 8));
+    CUDA_TRY(cudaMalloc(&g.chk_ticket, sizeof(unsigned int)));
+    CUDA_TRY(cudaMemset(g.chk_ticket, 0, sizeof(unsigned int)));
+    CUDA_TRY(cudaMalloc(&g.chk_out, sizeof(CheckPartial)));
+    CUDA_TRY(cudaHostAlloc(&g.chk_out_host, sizeof(CheckPartial), cudaHostAllocDefault));
+    CUDA_TRY(cudaHostAlloc(&g.async_err_host, sizeof(uint32_t), cudaHostAllocMapped));
+    *g.async_err_host = 0;
+    CUDA_TRY(cudaHostGetDevicePointer((void**)&g.async_err_dev, g.async_err_host, 0));
+    CUDA_TRY(cudaEventCreateWithFlags(&g.ev_done, cudaEventDisableTiming));
+    CUDA_TRY(configure_kernels(200 * 1024));
+    CUDA_TRY(occupancy(FLAVOUR_LDST, 0, &g.ctas_ldst));
+    CUDA_TRY(occupancy(FLAVOUR_TMA, (int)(o.tma_chunk * o.tma_stages), &g.ctas_tma));
+    if (g.ctas_ldst < 1) g.ctas_ldst = 1;
+    if (g.ctas_tma < 1) g.ctas_tma = 1;
+    CUDA_TRY(cudaDeviceSynchronize());
+    g.peer_ctl[rank] = g.ctl;
+    g.inited = true;
+    g.connected = false;
+    return P2P_SUCCESS;
+}
+
+size_t p2p_blob_bytes(void) { return kBlobBytes; }
+size_t p2p_register_blob_bytes(void) { return kRegBlobBytes; }
+
+int p2p_export(void* blob) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (!blob) return fail(P2P_INVALID_ARGUMENT, "null blob");
+    memset(blob, 0, kBlobBytes);
+    BootBlob b;
+    memset(&b, 0, sizeof b);
+    b.magic = kBlobMagic;
+    b.version = kBlobVersion;
+    b.rank = g.rank;
+    b.nranks = g.nranks;
+    b.host_hash = g.host_hash;
+    b.pid = (int32_t)getpid();
+    b.device = g.device;
+    b.eager_bytes = (uint64_t)g.opt.eager_bytes;
+    b.ctl_bytes = g.ctl_bytes;
+    CUDA_TRY(cudaDeviceGetPCIBusId(b.pci_bus_id, sizeof b.pci_bus_id, g.device));
+    if (g.nranks > 1) CUDA_TRY(cudaIpcGetMemHandle(&b.ctl_handle, g.ctl));
+    memcpy(blob, &b, sizeof b);
+    return P2P_SUCCESS;
+}
+
+int p2p_connect(const void* all_blobs) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (g.connected) return fail(P2P_INVALID_USAGE, "p2p_connect called twice");
+    if (!all_blobs) return fail(P2P_INVALID_ARGUMENT, "null blobs");
+    for (int r = 0; r < g.nranks; ++r) {
+        BootBlob b;
+        memcpy(&b, (const uint8_t*)all_blobs + (size_t)r * kBlobBytes, sizeof b);
+        if (b.magic != kBlobMagic || b.version != kBlobVersion)
+            return fail(P2P_INVALID_ARGUMENT, "blob %d is not a p2p bootstrap blob of this library version", r);
+        if (b.rank != r || b.nranks != g.nranks)
+            return fail(P2P_INVALID_ARGUMENT, "blob %d says rank %d of %d; blobs must be in rank order", r, b.rank, b.nranks);
+        if (b.host_hash != g.host_hash)
+            return fail(P2P_INVALID_USAGE,
+                        "rank %d runs on another host; NVLink peer mappings do not cross hosts (single-host engine)", r);
+        if (b.eager_bytes != (uint64_t)g.opt.eager_bytes)
+            return fail(P2P_INVALID_USAGE, "rank %d uses eager_bytes=%llu, this rank %lld; they must match", r,
+                        (unsigned long long)b.eager_bytes, g.opt.eager_bytes);
+        if (r == g.rank) continue;
+        if (b.ctl_bytes != g.ctl_bytes)
+            return fail(P2P_INTERNAL_ERROR, "rank %d control region is %llu bytes, mine %zu", r,
+                        (unsigned long long)b.ctl_bytes, g.ctl_bytes);
+        if (b.pid == (int32_t)getpid())
+            return fail(P2P_INVALID_USAGE, "rank %d lives in this process; the engine is one process per GPU", r);
+        std::string key;
+        cudaError_t e;
+        void* p = ipc_open(r, b.ctl_handle, &key, &e);
+        if (!p)
+            return fail(P2P_UNHANDLED_CUDA_ERROR,
+                        "cudaIpcOpenMemHandle for rank %d (pid %d, GPU %s) failed: %s — peers must share a PID/IPC "
+                        "namespace and be P2P-capable",
+                        r, b.pid, b.pci_bus_id, cudaGetErrorString(e));
+        g.peer_ctl[r] = (uint8_t*)p;
+    }
+    g.connected = true;
+    return P2P_SUCCESS;
+}
+
+int p2p_finalize(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.inited) return P2P_SUCCESS;
+    cudaSetDevice(g.device);
+    cudaDeviceSynchronize();
+    for (int w = 0; w < P2P_MAX_WINDOWS; ++w) {
+        Window& W = g.windows[w];
+        if (!W.used) continue;
+        for (int r = 0; r < g.nranks; ++r)
+            if (r != g.rank && !W.peer_handle[r].empty()) ipc_close(r, W.peer_handle[r]);
+        W = Window();
+    }
+    for (int r = 0; r < g.nranks; ++r) {
+        for (auto& kv : g.ipc_cache[r]) cudaIpcCloseMemHandle(kv.second.ptr);
+        g.ipc_cache[r].clear();
+        g.peer_ctl[r] = nullptr;
+        g.rdv_send_seq[r] = g.rdv_recv_seq[r] = g.ll_send_seq[r] = g.ll_recv_seq[r] = 0;
+    }
+    cudaFree(g.ctl);
+    cudaFree(g.arrive);
+    cudaFree(g.win_table);
+    cudaFree(g.chk_partials);
+    cudaFree(g.chk_ticket);
+    cudaFree(g.chk_out);
+    cudaFreeHost(g.chk_out_host);
+    cudaFreeHost(g.async_err_host);
+    if (g.ev_done) cudaEventDestroy(g.ev_done);
+    for (cudaEvent_t e : g.ev_pool) cudaEventDestroy(e);
+    g.ev_pool.clear();
+    g.ev_done = nullptr;
+    g.ctl = nullptr;
+    g.group_ops.clear();
+    g.group_depth = 0;
+    g.has_pending_reg = false;
+    g.inited = g.connected = false;
+    return P2P_SUCCESS;
+}
+
+int p2p_rank(void) { return g.inited ? g.rank : -1; }
+int p2p_nranks(void) { return g.inited ? g.nranks : 0; }
+
+int p2p_register_export(void* buf, size_t bytes, void* blob) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!blob) return fail(P2P_INVALID_ARGUMENT, "null blob");
+    // an export that was never imported (a peer failed in between) is simply superseded
+    memset(blob, 0, kRegBlobBytes);
+    RegBlob b;
+    memset(&b, 0, sizeof b);
+    b.magic = kBlobMagic;
+    if (buf && bytes) {
+        uint8_t* base = nullptr;
+        size_t asize = 0;
+        rc = allocation_range(buf, &base, &asize);
+        if (rc) return rc;
+        if ((uint8_t*)buf + bytes > base + asize)
+            return fail(P2P_INVALID_ARGUMENT, "window %p+%zu runs past its allocation (%p+%zu)", buf, bytes, base, asize);
+        b.has = 1;
+        b.bytes = bytes;
+        b.offset = (uint64_t)((uint8_t*)buf - base);
+        if (g.nranks > 1) CUDA_TRY(cudaIpcGetMemHandle(&b.handle, base));
+    }
+    memcpy(blob, &b, sizeof b);
+    g.pending_reg_buf = b.has ? buf : nullptr;
+    g.pending_reg_bytes = b.has ? bytes : 0;
+    g.has_pending_reg = true;
+    return P2P_SUCCESS;
+}
+
+int p2p_register_import(const void* all_blobs, int* window_id) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!g.has_pending_reg) return fail(P2P_INVALID_USAGE, "p2p_register_import without p2p_register_export");
+    if (!all_blobs || !window_id) return fail(P2P_INVALID_ARGUMENT, "null argument");
+    int w = -1;
+    for (int i = 0; i < P2P_MAX_WINDOWS; ++i)
+        if (!g.windows[i].used) { w = i; break; }
+    if (w < 0) return fail(P2P_INVALID_USAGE, "all %d windows are in use", P2P_MAX_WINDOWS);
+    Window W;
+    W.used = true;
+    W.base = (uint8_t*)g.pending_reg_buf;
+    W.bytes = g.pending_reg_bytes;
+    g.has_pending_reg = false;
+    std::vector<uint64_t> bases((size_t)g.nranks, 0);
+    for (int r = 0; r < g.nranks; ++r) {
+        RegBlob b;
+        memcpy(&b, (const uint8_t*)all_blobs + (size_t)r * kRegBlobBytes, sizeof b);
+        if (b.magic != kBlobMagic) return fail(P2P_INVALID_ARGUMENT, "register blob %d is malformed", r);
+        if (!b.has) continue;
+        if (r == g.rank) {
+            W.peer_base[r] = W.base;
+        } else {
+            cudaError_t e;
+            void* p = ipc_open(r, b.handle, &W.peer_handle[r], &e);
+            if (!p) {
+                for (int q = 0; q < r; ++q)
+                    if (q != g.rank && !W.peer_handle[q].empty()) ipc_close(q, W.peer_handle[q]);
+                return fail(P2P_UNHANDLED_CUDA_ERROR, "cudaIpcOpenMemHandle for rank %d's window failed: %s", r,
+                            cudaGetErrorString(e));
+            }
+            W.peer_base[r] = (uint8_t*)p + b.offset;
+        }
+        bases[(size_t)r] = (uint64_t)W.peer_base[r];
+    }
+    // device table: row r, column w = where rank r's part of window w is mapped here
+    for (int r = 0; r < g.nranks; ++r)
+        CUDA_TRY(cudaMemcpy(g.win_table + (size_t)r * P2P_MAX_WINDOWS + w, &bases[(size_t)r], sizeof(uint64_t),
+                            cudaMemcpyHostToDevice));
+    g.windows[w] = W;
+    *window_id = w;
+    return P2P_SUCCESS;
+}
+
+int p2p_deregister(int window_id) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    if (window_id < 0 || window_id >= P2P_MAX_WINDOWS || !g.windows[window_id].used)
+        return fail(P2P_INVALID_ARGUMENT, "window %d is not registered", window_id);
+    CUDA_TRY(cudaDeviceSynchronize());
+    Window& W = g.windows[window_id];
+    const uint64_t zero = 0;
+    for (int r = 0; r < g.nranks; ++r) {
+        if (r != g.rank && !W.peer_handle[r].empty()) ipc_close(r, W.peer_handle[r]);
+        CUDA_TRY(cudaMemcpy(g.win_table + (size_t)r * P2P_MAX_WINDOWS + window_id, &zero, sizeof zero,
+                            cudaMemcpyHostToDevice));
+    }
+    W = Window();
+    return P2P_SUCCESS;
+}
+
+int p2p_mem_alloc(void** ptr, size_t bytes) {
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (!ptr) return fail(P2P_INVALID_ARGUMENT, "null ptr");
+    CUDA_TRY(cudaSetDevice(g.device));
+    CUDA_TRY(cudaMalloc(ptr, bytes ? bytes : 1));
+    return P2P_SUCCESS;
+}
+
+int p2p_mem_free(void* ptr) {
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    CUDA_TRY(cudaFree(ptr));
+    return P2P_SUCCESS;
+}
+
+int p2p_send(const void* buf, size_t count, int dtype, int peer, p2p_stream_t stream) {
+    return enqueue(true, buf, count, dtype, peer, (cudaStream_t)stream);
+}
+
+int p2p_recv(void* buf, size_t count, int dtype, int peer, p2p_stream_t stream) {
+    return enqueue(false, buf, count, dtype, peer, (cudaStream_t)stream);
+}
+
+int p2p_group_start(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    g.group_depth++;
+    return P2P_SUCCESS;
+}
+
+int p2p_group_end(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    if (g.group_depth == 0) return fail(P2P_INVALID_USAGE, "p2p_group_end without p2p_group_start");
+    if (--g.group_depth > 0) return P2P_SUCCESS;
+    return launch_pending();
+}
+
+const char* p2p_get_error_string(int result) {
+    switch (result) {
+        case P2P_SUCCESS: return "no error";
+        case P2P_UNHANDLED_CUDA_ERROR: return "unhandled cuda error";
+        case P2P_SYSTEM_ERROR: return "unhandled system error";
+        case P2P_INTERNAL_ERROR: return "internal error";
+        case P2P_INVALID_ARGUMENT: return "invalid argument";
+        case P2P_INVALID_USAGE: return "invalid usage";
+        case P2P_REMOTE_ERROR: return "remote peer did not respond";
+        case P2P_IN_PROGRESS: return "operation in progress";
+        default: return "unknown result code";
+    }
+}
+
+const char* p2p_get_last_error(void) { return t_last_error; }
+
+int p2p_get_async_error(int* result) {
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (!result) return fail(P2P_INVALID_ARGUMENT, "null result");
+    const uint32_t code = *(volatile uint32_t*)g.async_err_host;
+    if (code == AERR_NONE) {
+        *result = P2P_SUCCESS;
+    } else {
+        static const char* const what[] = {"", "send: receiver never posted", "recv: payload never completed",
+                                           "eager recv: data never arrived", "eager send: ring slot never freed",
+                                           "send: receiver posted an unknown window"};
+        *result = code == AERR_BAD_WINDOW ? P2P_INVALID_USAGE : P2P_REMOTE_ERROR;
+        fail(*result, "device reported: %s (code %u, timeout %lld ms)", code < 6 ? what[code] : "?", code,
+             g.opt.timeout_ms);
+    }
+    return P2P_SUCCESS;
+}
+
+static long long* option_slot(const char* name) {
+    Options& o = g.opt;
+    if (!strcmp(name, "path")) return &o.path;
+    if (!strcmp(name, "nblocks")) return &o.nblocks;
+    if (!strcmp(name, "self_nblocks")) return &o.self_nblocks;
+    if (!strcmp(name, "eager_bytes")) return &o.eager_bytes;
+    if (!strcmp(name, "timeout_ms")) return &o.timeout_ms;
+    if (!strcmp(name, "vec_bytes")) return &o.vec_bytes;
+    if (!strcmp(name, "tma_chunk")) return &o.tma_chunk;
+    if (!strcmp(name, "tma_stages")) return &o.tma_stages;
+    if (!strcmp(name, "tma_min_bytes")) return &o.tma_min_bytes;
+    return nullptr;
+}
+
+int p2p_set_option(const char* name, long long value) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (!name) return fail(P2P_INVALID_ARGUMENT, "null option name");
+    long long* slot = option_slot(name);
+    if (!slot) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
+    if (!strcmp(name, "eager_bytes")) {
+        // the rings were sized in p2p_init; the limit can only shrink afterwards, and on every rank alike
+        if (value < 0 || (size_t)value * 2 > g.ll_slot_bytes)
+            return fail(P2P_INVALID_ARGUMENT, "eager_bytes %lld exceeds the ring slot (%zu bytes); set P2P_EAGER_BYTES before p2p_init",
+                        value, g.ll_slot_bytes / 2);
+    } else if (!strcmp(name, "path")) {
+        if (value < 0 || value > 3) return fail(P2P_INVALID_ARGUMENT, "path must be 0..3");
+    } else if (!strcmp(name, "vec_bytes")) {
+        if (value != 16 && value != 32) return fail(P2P_INVALID_ARGUMENT, "vec_bytes must be 16 or 32");
+    } else if (!strcmp(name, "tma_chunk") || !strcmp(name, "tma_stages")) {
+        long long chunk = !strcmp(name, "tma_chunk") ? value : g.opt.tma_chunk;
+        long long stages = !strcmp(name, "tma_stages") ? value : g.opt.tma_stages;
+        if (chunk < 1024 || chunk % 16 || chunk > 128 * 1024 || stages < 2 || stages > kTmaMaxStages ||
+            chunk * stages > 200 * 1024)
+            return fail(P2P_INVALID_ARGUMENT, "tma ring %lld x %lld bytes is not allowed (<= 200 KiB, 2..%d stages)",
+                        stages, chunk, kTmaMaxStages);
+        *slot = value;
+        int n = 1;
+        if (occupancy(FLAVOUR_TMA, (int)(g.opt.tma_chunk * g.opt.tma_stages), &n) == cudaSuccess && n >= 1) g.ctas_tma = n;
+        return P2P_SUCCESS;
+    } else if (value < 0 && strcmp(name, "tma_min_bytes")) {
+        return fail(P2P_INVALID_ARGUMENT, "option '%s' must be >= 0", name);
+    }
+    *slot = value;
+    return P2P_SUCCESS;
+}
+
+int p2p_get_option(const char* name, long long* value) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (!name || !value) return fail(P2P_INVALID_ARGUMENT, "null argument");
+    if (!strcmp(name, "sm_count")) { *value = g.sm_count; return P2P_SUCCESS; }
+    if (!strcmp(name, "ctas_per_sm_ldst")) { *value = g.ctas_ldst; return P2P_SUCCESS; }
+    if (!strcmp(name, "ctas_per_sm_tma")) { *value = g.ctas_tma; return P2P_SUCCESS; }
+    long long* slot = option_slot(name);
+    if (!slot) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
+    *value = *slot;
+    return P2P_SUCCESS;
+}
+
+int p2p_query_plan(size_t bytes, int peer, int* path, int* nblocks) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    if (peer < 0 || peer >= g.nranks) return fail(P2P_INVALID_ARGUMENT, "peer %d out of range", peer);
+    Plan p = plan_for(bytes, peer);
+    if (path) *path = p.path;
+    if (nblocks) *nblocks = p.nblocks;
+    return P2P_SUCCESS;
+}
+
+int p2p_pattern_fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, p2p_stream_t stream) {
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (bytes && !buf) return fail(P2P_INVALID_ARGUMENT, "null buffer");
+    CUDA_TRY(launch_pattern_fill(buf, bytes, pattern_key(seed, rank, iter), g.sm_count, (cudaStream_t)stream));
+    return P2P_SUCCESS;
+}
+
+static int run_check(const void* buf, size_t bytes, uint64_t key, int check, cudaStream_t stream,
+                     uint64_t* mismatches, uint64_t* first_bad, uint64_t* digest) {
+    if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
+    if (bytes && !buf) return fail(P2P_INVALID_ARGUMENT, "null buffer");
+    std::lock_guard<std::mutex> lk(g.mu);  // one scratch area
+    CUDA_TRY(launch_pattern_check(buf, bytes, key, check, g.sm_count, g.chk_partials, g.chk_ticket, g.chk_out, stream));
+    CUDA_TRY(cudaMemcpyAsync(g.chk_out_host, g.chk_out, sizeof(CheckPartial), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    if (mismatches) *mismatches = g.chk_out_host->mismatches;
+    if (first_bad) *first_bad = g.chk_out_host->first_bad;
+    if (digest) *digest = g.chk_out_host->digest;
+    return P2P_SUCCESS;
+}
+
+int p2p_pattern_check(const void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, p2p_stream_t stream,
+                      uint64_t* mismatches, uint64_t* first_bad, uint64_t* digest) {
+    return run_check(buf, bytes, pattern_key(seed, rank, iter), 1, (cudaStream_t)stream, mismatches, first_bad, digest);
+}
+
+int p2p_digest(const void* buf, size_t bytes, p2p_stream_t stream, uint64_t* digest) {
+    return run_check(buf, bytes, 0, 0, (cudaStream_t)stream, nullptr, nullptr, digest);
+}
+
+}  // extern "C"

@@ -1,0 +1,223 @@
+// Kernels of the transfer engine and their launch wrappers (compiled for sm_100a only).
+#include "p2p_internal.h"
+#include "p2p_tma.cuh"
+
+namespace p2p {
+
+// ------------------------------------------------------------------ group kernels
+
+// ld/st flavour: 512-thread CTAs, payload moves through registers as 16- or 32-byte
+// coalesced vectors (LDG.E.128/256 + STG.E.128/256 to the peer-mapped address).
+__global__ void __launch_bounds__(kLdstThreads, 2)
+p2p_group_kernel_ldst(const __grid_constant__ GroupArgs a) {
+    __shared__ uint64_t slot;
+    const uint32_t bid = blockIdx.x;
+    if (a.n_ctrl && bid == 0) { run_ctrl(a); return; }
+    const OpDesc* op = find_op(a, bid);
+    if (!op) return;
+    const uint32_t part = bid - op->first_block;
+    switch (op->kind) {
+        case OP_SEND_RDV: {
+            uint8_t* dst = send_wait_post(a, *op, &slot);
+            if (!dst) return;
+            copy_bytes(dst, (const uint8_t*)op->local, op->nbytes, part, op->nblocks, a.vec_bytes);
+            send_signal_done(*op);
+            break;
+        }
+        case OP_SEND_LL: ll_send(a, *op, &slot); break;
+        case OP_RECV_LL: ll_recv(a, *op); break;
+        default: break;
+    }
+}
+
+// TMA flavour: 128-thread CTAs, payload staged global -> shared -> peer global by
+// cp.async.bulk (UBLKCP), two elected threads drive the ring.
+__global__ void __launch_bounds__(kTmaThreads, 1)
+p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
+    extern __shared__ __align__(128) uint8_t smem_ring[];
+    __shared__ uint64_t slot;
+    __shared__ __align__(8) uint64_t full[kTmaMaxStages];
+    __shared__ __align__(8) uint64_t empty[kTmaMaxStages];
+    const uint32_t bid = blockIdx.x;
+    if (a.n_ctrl && bid == 0) { run_ctrl(a); return; }
+    const OpDesc* op = find_op(a, bid);
+    if (!op) return;
+    const uint32_t part = bid - op->first_block;
+    switch (op->kind) {
+        case OP_SEND_RDV: {
+            if (threadIdx.x == 0) {
+                for (uint32_t i = 0; i < a.tma_stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                fence_proxy_async();
+            }
+            uint8_t* dst = send_wait_post(a, *op, &slot);  // contains the __syncthreads that publishes the inits
+            if (!dst) return;
+            const uint8_t* src = (const uint8_t*)op->local;
+            if ((((uint64_t)dst ^ (uint64_t)src) & 15) == 0)
+                tma_push(dst, src, op->nbytes, part, op->nblocks, a.tma_chunk, a.tma_stages, smem_ring, full, empty);
+            else
+                copy_bytes(dst, src, op->nbytes, part, op->nblocks, 16);
+            send_signal_done(*op);
+            break;
+        }
+        case OP_SEND_LL: ll_send(a, *op, &slot); break;
+        case OP_RECV_LL: ll_recv(a, *op); break;
+        default: break;
+    }
+}
+
+cudaError_t configure_kernels(int max_tma_smem) {
+    return cudaFuncSetAttribute(p2p_group_kernel_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, max_tma_smem);
+}
+
+cudaError_t occupancy(int flavour, int dyn_smem, int* ctas_per_sm) {
+    if (flavour == FLAVOUR_TMA)
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, p2p_group_kernel_tma, kTmaThreads, dyn_smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, p2p_group_kernel_ldst, kLdstThreads, 0);
+}
+
+cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, int dyn_smem, cudaStream_t stream) {
+    if (flavour == FLAVOUR_TMA)
+        p2p_group_kernel_tma<<<grid, kTmaThreads, dyn_smem, stream>>>(args);
+    else
+        p2p_group_kernel_ldst<<<grid, kLdstThreads, 0, stream>>>(args);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ pattern / digest kernels
+
+constexpr int kPatThreads = 256;
+
+__global__ void __launch_bounds__(kPatThreads)
+pattern_fill_kernel(uint8_t* buf, size_t nbytes, uint64_t key) {
+    const size_t nwords = (nbytes + 7) / 8;
+    const bool aligned = ((uint64_t)buf & 7) == 0;
+    for (size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += (size_t)gridDim.x * blockDim.x) {
+        const uint64_t v = pattern_word(key, w);
+        const size_t off = w * 8;
+        if (aligned && off + 8 <= nbytes) {
+            *(uint64_t*)(buf + off) = v;
+        } else {
+            const int n = nbytes - off < 8 ? (int)(nbytes - off) : 8;
+            for (int i = 0; i < n; ++i) buf[off + i] = (uint8_t)(v >> (8 * i));
+        }
+    }
+}
+
+__device__ __forceinline__ uint64_t load_word_le(const uint8_t* buf, size_t off, size_t nbytes, bool aligned) {
+    if (aligned && off + 8 <= nbytes) return *(const uint64_t*)(buf + off);
+    uint64_t v = 0;
+    const int n = nbytes - off < 8 ? (int)(nbytes - off) : 8;
+    for (int i = 0; i < n; ++i) v |= (uint64_t)buf[off + i] << (8 * i);
+    return v;
+}
+
+// One pass: mismatching bytes vs the pattern (if check), first bad offset, digest.
+// Per-CTA partials go to `partials`; the last CTA to finish folds them into `out`.
+__global__ void __launch_bounds__(kPatThreads)
+pattern_check_kernel(const uint8_t* buf, size_t nbytes, uint64_t key, int check, CheckPartial* partials,
+                     unsigned int* ticket, CheckPartial* out) {
+    const size_t nwords = (nbytes + 7) / 8;
+    const bool aligned = ((uint64_t)buf & 7) == 0;
+    uint64_t bad = 0, first = UINT64_MAX, dig = 0;
+    for (size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += (size_t)gridDim.x * blockDim.x) {
+        const size_t off = w * 8;
+        const uint64_t v = load_word_le(buf, off, nbytes, aligned);
+        dig += digest_term(v, w);
+        if (check) {
+            uint64_t want = pattern_word(key, w);
+            if (nbytes - off < 8) want &= (1ull << (8 * (nbytes - off))) - 1;
+            uint64_t x = v ^ want;
+            if (x) {
+                // fold every differing byte to its low bit, count, and locate the first
+                uint64_t m = x | (x >> 4);
+                m |= m >> 2;
+                m |= m >> 1;
+                m &= 0x0101010101010101ull;
+                bad += __popcll(m);
+                const uint64_t pos = off + ((__ffsll((long long)m) - 1) >> 3);
+                first = pos < first ? pos : first;
+            }
+        }
+    }
+    // CTA reduction
+    __shared__ uint64_t s_bad[kPatThreads / 32], s_first[kPatThreads / 32], s_dig[kPatThreads / 32];
+    for (int o = 16; o > 0; o >>= 1) {
+        bad += __shfl_xor_sync(0xffffffffu, bad, o);
+        dig += __shfl_xor_sync(0xffffffffu, dig, o);
+        const uint64_t f = __shfl_xor_sync(0xffffffffu, first, o);
+        first = f < first ? f : first;
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { s_bad[warp] = bad; s_first[warp] = first; s_dig[warp] = dig; }
+    __syncthreads();
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < kPatThreads / 32; ++i) {
+            bad += s_bad[i];
+            dig += s_dig[i];
+            first = s_first[i] < first ? s_first[i] : first;
+        }
+        partials[blockIdx.x].mismatches = bad;
+        partials[blockIdx.x].first_bad = first;
+        partials[blockIdx.x].digest = dig;
+        __threadfence();
+        const unsigned int t = atomicInc(ticket, gridDim.x - 1);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    bad = 0; first = UINT64_MAX; dig = 0;
+    for (unsigned int i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+        const volatile CheckPartial* p = &partials[i];
+        bad += p->mismatches;
+        dig += p->digest;
+        const uint64_t f = p->first_bad;
+        first = f < first ? f : first;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        bad += __shfl_xor_sync(0xffffffffu, bad, o);
+        dig += __shfl_xor_sync(0xffffffffu, dig, o);
+        const uint64_t f = __shfl_xor_sync(0xffffffffu, first, o);
+        first = f < first ? f : first;
+    }
+    __syncthreads();
+    if (lane == 0) { s_bad[warp] = bad; s_first[warp] = first; s_dig[warp] = dig; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < kPatThreads / 32; ++i) {
+            bad += s_bad[i];
+            dig += s_dig[i];
+            first = s_first[i] < first ? s_first[i] : first;
+        }
+        out->mismatches = bad;
+        out->first_bad = first < nbytes ? first : nbytes;
+        out->digest = digest_finish(dig, nbytes);
+    }
+}
+
+uint32_t pattern_grid(size_t nbytes, int sm_count) {
+    const size_t nwords = (nbytes + 7) / 8;
+    size_t want = (nwords + (size_t)kPatThreads * 4 - 1) / ((size_t)kPatThreads * 4);
+    const size_t cap = (size_t)sm_count * 8;
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    return (uint32_t)want;
+}
+
+cudaError_t launch_pattern_fill(void* buf, size_t nbytes, uint64_t key, int sm_count, cudaStream_t stream) {
+    if (nbytes == 0) return cudaSuccess;
+    pattern_fill_kernel<<<pattern_grid(nbytes, sm_count), kPatThreads, 0, stream>>>((uint8_t*)buf, nbytes, key);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pattern_check(const void* buf, size_t nbytes, uint64_t key, int check, int sm_count,
+                                 CheckPartial* partials, unsigned int* ticket, CheckPartial* out,
+                                 cudaStream_t stream) {
+    pattern_check_kernel<<<pattern_grid(nbytes, sm_count), kPatThreads, 0, stream>>>(
+        (const uint8_t*)buf, nbytes, key, check, partials, ticket, out);
+    return cudaGetLastError();
+}
+
+}  // namespace p2p

@@ -1,0 +1,58 @@
+// p2p_matrix — the matrix benchmark of AmadeusChan/test-nccl-p2p, with the B200 transfer
+// engine where the reference calls NCCL.  Same launch (`mpirun -n N p2p_matrix`, reference
+// README.md:5), same report; with no arguments it measures what the reference measures the
+// way the reference measures it.  The driver is in matrix_driver.hpp; this file is only the
+// engine's backend, i.e. the lines of p2p_matrix.cc that named ncclXxx.
+#include "matrix_driver.hpp"
+#include "p2p.h"
+#include "p2p_mpi.h"
+
+struct EngineBackend {
+    const char* name() const { return "engine"; }
+
+    // replaces ncclGetUniqueId + MPI_Bcast + ncclCommInitRank (p2p_matrix.cc:115-120)
+    void init(int, int, int device) { P2PCHECK(p2p_init_mpi(MPI_COMM_WORLD, device)); }
+
+    // the reference's cudaMalloc'd buffers stay as they are (p2p_matrix.cc:127-128); the one
+    // added step is making the receive buffer a window peers can store into
+    void buffers(void*, size_t, void* recv, size_t rbytes) {
+        int win = -1;
+        P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, recv, rbytes, &win));
+    }
+
+    // ncclSend / ncclRecv with ncclInt8 (p2p_matrix.cc:157-161, 165-169)
+    void send(const void* buf, size_t bytes, int peer, cudaStream_t s) { P2PCHECK(p2p_send(buf, bytes, P2P_INT8, peer, s)); }
+    void recv(void* buf, size_t bytes, int peer, cudaStream_t s) { P2PCHECK(p2p_recv(buf, bytes, P2P_INT8, peer, s)); }
+    void group_start() { P2PCHECK(p2p_group_start()); }  // p2p_matrix.cc:212
+    void group_end() { P2PCHECK(p2p_group_end()); }      // p2p_matrix.cc:227
+
+    void fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s) {
+        P2PCHECK(p2p_pattern_fill(buf, bytes, seed, rank, iter, s));
+    }
+    uint64_t check(const void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s,
+                   uint64_t* digest) {
+        uint64_t bad = 0, first = 0;
+        P2PCHECK(p2p_pattern_check(buf, bytes, seed, rank, iter, s, &bad, &first, digest));
+        int aerr = 0;
+        P2PCHECK(p2p_get_async_error(&aerr));
+        if (aerr != P2P_SUCCESS) {
+            printf("Failed, P2P async error '%s' (%s)\n", p2p_get_error_string(aerr), p2p_get_last_error());
+            exit(EXIT_FAILURE);
+        }
+        return bad;
+    }
+
+    void finalize() {
+        int aerr = 0;
+        if (p2p_get_async_error(&aerr) == P2P_SUCCESS && aerr != P2P_SUCCESS) {
+            printf("Failed, P2P async error '%s' (%s)\n", p2p_get_error_string(aerr), p2p_get_last_error());
+            exit(EXIT_FAILURE);
+        }
+        P2PCHECK(p2p_finalize());  // ncclCommDestroy, p2p_matrix.cc:270
+    }
+};
+
+int main(int argc, char** argv) {
+    EngineBackend be;
+    return bench::run_main(be, argc, argv);
+}
