@@ -74,7 +74,11 @@ mpirun-link: $(MPI_DEP)
 oracle: $(MPI_DEP) $(BUILD)/libb200p2p.a
 	$(MAKE) -C oracle
 
-tests: $(BUILD)/minimpi_selftest
+tests: $(BUILD)/minimpi_selftest $(BUILD)/driver_unit
+
+$(BUILD)/driver_unit: tests/csrc/driver_unit.cc $(PKG)/host/matrix_driver.hpp $(MPI_DEP)
+	@mkdir -p $(BUILD)
+	$(NVCC) -std=c++17 -O1 -I$(PKG)/host $(MPI_INC) $< $(MPI_LIB) -o $@
 
 $(BUILD)/minimpi_selftest: tests/csrc/minimpi_selftest.c third_party/minimpi/libmpi.a
 	@mkdir -p $(BUILD)

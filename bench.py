@@ -1,0 +1,461 @@
+#!/usr/bin/env python
+"""bench.py — the measurement contract for the transfer engine.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--size BYTES]
+
+A STEP is one pass of the hot path: every GPU sends one message of `size` bytes (default the
+256 MiB of BASELINE.json's configs[1]) to the next GPU and receives one from the previous,
+as one grouped p2p_send/p2p_recv pair per rank (the reference's call shape,
+p2p_matrix.cc:212-228).  With N = 1 the "next GPU" is the GPU itself: a local HBM copy through
+the same kernel, flags and C ABI.  N > 1 is launched by the driver as
+`python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...`; ranks are
+independent (no data-path collective), so scaling is weak.
+
+  value     whole-job payload GB/s, buffers resident in HBM, CUDA events on the launch stream,
+            barrier + synchronize either side, max over ranks
+  e2e       the same step with the payload starting and ending in pinned HOST memory:
+            H2D copy, transfer, D2H copy inside the timed region, through the public C ABI
+  roofline  the step IS one kernel (p2p_group_kernel_*): algorithmic bytes per launch divided by
+            the event-timed launch duration; N = 1 against measured HBM copy bandwidth
+            (read + write bytes), N > 1 against NVLink 5's 900 GB/s per direction
+  cpu_baseline   the MPI host-memory send/recv path (oracle/_ref/mpi_host_p2p) on 2 host cores
+  --impl reference   the reference's own path — libnccl's ncclSend/ncclRecv driven by the
+            reference's loop (oracle/_ref/p2p_matrix_nccl) — on the same step, same timing
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+MPIRUN = os.path.join(ROOT, "build", "mpirun")
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+LINK_GBPS = 900.0          # NVLink 5 per direction per GPU (BASELINE.json)
+LINK_MEASURED_GBPS = 770.0  # peer-copy figure in /opt/skills/guides/B200_PROFILING.md
+METRIC = "P2P payload bandwidth, ring step (each GPU sends one message to the next), whole job"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--size", type=int, default=256 << 20)
+    ap.add_argument("--no-extras", action="store_true", help="skip latency / all-pairs / NCCL side measurements")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+# ------------------------------------------------------------------ clocks (NVML)
+
+REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+           0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+           0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+
+class Clocks:
+    """Samples SM clock and throttle reasons of one GPU while a timed region runs."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                try:
+                    phys = int(vis.split(",")[index])
+                except Exception:
+                    phys = index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # no NVML: report that instead of inventing numbers
+            self.err = repr(e)
+
+    def sample(self):
+        if not self.ok:
+            return
+        try:
+            self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+            fn = getattr(self.nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or self.nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            mask = fn(self.h)
+            for bit, name in REASONS.items():
+                if mask & bit and name != "gpu_idle":
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def summary(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0,
+                    "note": "NVML unavailable" if not self.ok else "no sample landed inside the timed region"}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------ baselines run as subprocesses
+
+def run_json(cmd, timeout):
+    """Run a benchmark binary that writes JSON lines to --json FILE; return the records."""
+    with tempfile.NamedTemporaryFile("r", suffix=".json", delete=False) as tf:
+        path = tf.name
+    try:
+        proc = subprocess.run(cmd + ["--json", path], cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout)
+        if proc.returncode != 0:
+            return None, proc.stdout[-1500:]
+        with open(path) as f:
+            return [json.loads(l) for l in f if l.strip()], proc.stdout
+    except Exception as e:
+        return None, repr(e)
+    finally:
+        try:
+            os.unlink(path)
+        except OSError:
+            pass
+
+
+def cpu_baseline(size: int):
+    """MPI host-memory send/recv of the same message between two ranks on the host cores.
+    Bounded sample: enough messages for roughly ten seconds."""
+    exe = os.path.join(REF_DIR, "mpi_host_p2p")
+    if not (os.path.exists(exe) and os.path.exists(MPIRUN)):
+        return {"value": None, "unit": "GB/s", "cores": 2, "kind": "port", "sample": "oracle/_ref/mpi_host_p2p not built"}
+    probe, _ = run_json([MPIRUN, "-n", "2", exe, "--size", str(size), "--iters", "3", "--mode", "uni", "--first-pair"], 300)
+    if not probe:
+        return {"value": None, "unit": "GB/s", "cores": 2, "kind": "port", "sample": "mpi_host_p2p failed"}
+    per_msg = probe[0]["seconds"]
+    iters = max(5, min(400, int(10.0 / max(per_msg, 1e-6))))
+    recs, _ = run_json([MPIRUN, "-n", "2", exe, "--size", str(size), "--iters", str(iters), "--warmup", "2", "--mode", "uni", "--first-pair"], 600)
+    if not recs:
+        return {"value": None, "unit": "GB/s", "cores": 2, "kind": "port", "sample": "mpi_host_p2p failed"}
+    r = recs[0]
+    return {"value": round(r["GBps"], 3), "unit": "GB/s", "cores": 2, "kind": "port",
+            "host_cores": r.get("host_cores"), "transport": r.get("transport"),
+            "sample": f"{iters} messages of {size} bytes rank 0 -> rank 1 through host memory (MPI_Send/MPI_Recv, "
+                      f"reference loop shape p2p_matrix.cc:141-186), {r['us']:.0f} us each"}
+
+
+def nccl_run(n: int, mode: str, size: int, iters: int, warmup: int, extra=(), timeout=900):
+    exe = os.path.join(REF_DIR, "p2p_matrix_nccl")
+    if not (os.path.exists(exe) and os.path.exists(MPIRUN)):
+        return None, "oracle/_ref/p2p_matrix_nccl not built"
+    return run_json([MPIRUN, "-n", str(n), exe, "--mode", mode, "--size", str(size), "--iters", str(iters), "--warmup", str(warmup),
+                     "--timing", "dev", *extra], timeout)
+
+
+# ------------------------------------------------------------------ the reference arm
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0  # rank 0 alone drives all N GPUs through the MPI launcher
+    n = args.gpus
+    steps, warm = args.steps, max(args.warmup, 3)
+    recs, log = nccl_run(n, "ring", args.size, steps, warm)
+    if not recs:
+        print(json.dumps({"impl": "reference", "unavailable": f"NCCL harness did not run: {str(log)[-300:]}"}))
+        return 0
+    ring = [r for r in recs if r["mode"] == "ring"][0]
+    e2e_steps = max(3, min(steps, 40))
+    erecs, _ = nccl_run(n, "ring", args.size, e2e_steps, 3, extra=["--e2e"])
+    e2e = [r for r in (erecs or []) if r["mode"] == "ring_e2e"]
+    base = cpu_baseline(args.size) if n == 1 else None
+    line = {
+        "impl": "reference",
+        "metric": METRIC, "value": round(ring["GBps"], 3), "unit": "GB/s", "n_gpus": n, "steps": steps, "warmup": warm,
+        "ms_per_step": round(ring["seconds"] * 1e3, 6), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"ring step, {args.size} bytes per GPU (BASELINE configs[1] message size)", "bytes": args.size,
+                   "what": "reference's own path: ncclSend/ncclRecv from libnccl 2.27.3 in the reference's loop "
+                           "(oracle/_ref/p2p_matrix_nccl), launched by mpirun on the same GPUs",
+                   "l2": "message larger than L2 (126 MB)" if args.size > (126 << 20) else "message fits L2"},
+        "e2e": {"value": round(e2e[0]["GBps"], 3) if e2e else None, "unit": "GB/s",
+                "h2d_bytes_per_step": args.size * n if e2e else 0, "d2h_bytes_per_step": args.size * n if e2e else 0,
+                "steps": e2e_steps, "note": "same H2D + transfer + D2H step as the engine arm, NCCL doing the transfer"},
+        "gpu_launches": 0,
+    }
+    if base is not None:
+        line["cpu_baseline"] = base
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------ the engine arm
+
+def engine_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            # convenience: relaunch ourselves the way the driver would
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:]
+            return subprocess.call(cmd)
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: the engine has no CPU path")
+    torch.cuda.set_device(local)
+    p2p = importlib.import_module("test-nccl-p2p_b200")
+    host_group = None
+    if world > 1:
+        # torch.distributed is plumbing only (bootstrap blobs, barriers, max over ranks): gloo is enough,
+        # the payload never goes through it
+        dist.init_process_group("gloo")
+        host_group = dist.group.WORLD
+    gather = p2p.torch_allgather(host_group) if world > 1 else (lambda b: [b])
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=host_group)
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=host_group)
+        return float(t.item())
+
+    B = args.size
+    K, W = args.steps, max(args.warmup, 3)
+    right, left = (rank + 1) % world, (rank - 1) % world
+    p2p.init(rank, world, local, gather)
+    src, dst = p2p.DeviceBuffer(B), p2p.DeviceBuffer(B + 256)
+    p2p.register(dst.ptr, dst.nbytes, gather)
+    stream = torch.cuda.Stream()
+    clocks = Clocks(local)
+
+    def step():
+        with p2p.group():
+            p2p.recv(dst.ptr, B, p2p.INT8, left, stream)
+            p2p.send(src.ptr, B, p2p.INT8, right, stream)
+
+    def verify(it):
+        p2p.pattern_fill(src.ptr, B, 0x5EED0001, rank, it, stream)
+        dst.tensor().fill_(0xA5)
+        barrier()
+        step()
+        bad, first, dig = p2p.pattern_check(dst.ptr, B, 0x5EED0001, left, it, stream)
+        p2p.raise_async_error()
+        if bad:
+            raise SystemExit(f"rank {rank}: transfer is wrong: {bad} bytes differ, first at {first}")
+        return dig
+
+    def timed(fn, steps):
+        """barrier+sync, `steps` calls enqueued back to back, events on the launch stream, clocks sampled
+        while the GPU works, barrier+sync; returns seconds for all steps (max over ranks)."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        while not e1.query():
+            clocks.sample()
+            time.sleep(0.002)
+        stream.synchronize()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1) * 1e-3)
+
+    digest_before = verify(1)
+    plan = p2p.query_plan(B, right)
+    for _ in range(W):
+        step()
+    stream.synchronize()
+    total = timed(step, K)
+    p2p.raise_async_error()
+    digest_after = verify(2)
+    per_step = total / K
+    value = world * B / per_step / 1e9
+
+    # ---- e2e: payload starts and ends in pinned host memory, copies inside the timed region
+    hsrc = torch.empty(B, dtype=torch.uint8).pin_memory()
+    hdst = torch.empty(B, dtype=torch.uint8).pin_memory()
+    hsrc.fill_(0x3C)
+    src_t, dst_t = src.tensor(), dst.tensor()[:B]
+
+    def step_e2e():
+        with torch.cuda.stream(stream):
+            src_t.copy_(hsrc, non_blocking=True)
+        step()
+        with torch.cuda.stream(stream):
+            hdst.copy_(dst_t, non_blocking=True)
+
+    e2e_steps = max(3, min(K, 40))
+    for _ in range(3):
+        step_e2e()
+    stream.synchronize()
+    e2e_total = timed(step_e2e, e2e_steps)
+    e2e_ok = bool(hdst[:4096].eq(0x3C).all().item() and hdst[-4096:].eq(0x3C).all().item())
+    e2e_value = world * B / (e2e_total / e2e_steps) / 1e9
+
+    # ---- side measurements the north star asks to sit next to the number (not part of `value`)
+    extras = {}
+    if not args.no_extras:
+        extras = side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks)
+
+    peaks, peak_kind = measured_peaks()
+    if world == 1:
+        roof = {"bound": "hbm", "achieved": round(2 * B / per_step / 1e9, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "peak_kind": f"{peak_kind} HBM copy (read+write bytes)", "traffic": TRAFFIC_PER_LAUNCH.get("local")}
+    else:
+        roof = {"bound": "nvlink", "achieved": round(B / per_step / 1e9, 2), "peak": LINK_GBPS, "unit": "GB/s",
+                "peak_kind": f"nominal NVLink 5 per direction per GPU; measured peer copy on this pool {LINK_MEASURED_GBPS}",
+                "traffic": TRAFFIC_PER_LAUNCH.get("peer")}
+    roof["frac"] = round(roof["achieved"] / roof["peak"], 4)
+    roof["kernel"] = "p2p_group_kernel_tma" if plan[0] == p2p.PATH_TMA else "p2p_group_kernel_ldst"
+    roof["algorithmic_bytes_per_launch"] = (2 if world == 1 else 1) * B
+    roof["ctas"] = plan[1]
+
+    torch.cuda.synchronize()
+    p2p.finalize()
+    if world > 1:
+        dist.barrier(group=host_group)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(per_step * 1e3, 6), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": f"ring step, {B} bytes per GPU (BASELINE configs[1] message size)"
+                                   + ("; N=1: local HBM copy through the same send/recv kernel" if world == 1 else ""),
+                       "bytes": B, "l2": "message larger than L2 (126 MB), no flush needed" if B > (126 << 20) else "message fits L2",
+                       "path": {1: "ldst", 2: "tma", 4: "eager"}.get(plan[0], str(plan[0])), "ctas": plan[1]},
+            "clocks": clocks.summary(),
+            "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": B * world, "d2h_bytes_per_step": B * world,
+                    "steps": e2e_steps, "payload_intact": e2e_ok},
+            "gpu_launches": K * world,
+            "roofline": roof,
+            "parity": {"digest_before": f"{digest_before:#018x}", "digest_after": f"{digest_after:#018x}", "mismatches": 0},
+        }
+        if world == 1:
+            line["cpu_baseline"] = cpu_baseline(B)
+        if extras:
+            line["extras"] = extras
+        if not args.no_extras:
+            recs, log = nccl_run(world, "ring", B, min(K, 200), 5)
+            ring = [r for r in (recs or []) if r["mode"] == "ring"]
+            line["nccl_same_run"] = ({"value": round(ring[0]["GBps"], 3), "unit": "GB/s", "ms_per_step": round(ring[0]["seconds"] * 1e3, 6),
+                                      "what": "ncclSend/ncclRecv ring step, libnccl 2.27.3, device timing"} if ring
+                                     else {"unavailable": str(log)[-200:]})
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier(group=host_group)
+        dist.destroy_process_group()
+    return 0
+
+
+# dram bytes per launch from the committed ncu captures (profiles/); None until a capture exists
+TRAFFIC_PER_LAUNCH = {"local": None, "peer": None}
+
+
+def side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks):
+    """8-byte one-way latency, single-pair uni/bidir bandwidth and all-pairs aggregate (N >= 2)."""
+    out = {}
+    if world < 2:
+        return out
+
+    def events_around(fn, iters, active=True):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        sec = 0.0
+        if active:
+            e0.record(stream)
+            for _ in range(iters):
+                fn()
+            e1.record(stream)
+            stream.synchronize()
+            sec = e0.elapsed_time(e1) * 1e-3
+        barrier()
+        return max_over_ranks(sec)
+
+    pair = rank in (0, 1)
+    peer = 1 - rank if pair else 0
+
+    def pingpong(n):
+        if rank == 0:
+            p2p.send(src.ptr, n, p2p.INT8, 1, stream)
+            p2p.recv(dst.ptr, n, p2p.INT8, 1, stream)
+        elif rank == 1:
+            p2p.recv(dst.ptr, n, p2p.INT8, 0, stream)
+            p2p.send(src.ptr, n, p2p.INT8, 0, stream)
+
+    events_around(lambda: pingpong(8), 50, pair)
+    t = events_around(lambda: pingpong(8), 2000, pair)
+    out["latency_8B_oneway_us"] = round(t / 2000 / 2 * 1e6, 3)
+
+    def uni(n):
+        if rank == 0:
+            p2p.send(src.ptr, n, p2p.INT8, 1, stream)
+        elif rank == 1:
+            p2p.recv(dst.ptr, n, p2p.INT8, 0, stream)
+
+    def bidir(n):
+        with p2p.group():
+            p2p.send(src.ptr, n, p2p.INT8, peer, stream)
+            p2p.recv(dst.ptr, n, p2p.INT8, peer, stream)
+
+    for name, n in (("64MiB", 64 << 20), ("256MiB", 256 << 20)):
+        if n > B:
+            continue
+        events_around(lambda: uni(n), 5, pair)
+        t = events_around(lambda: uni(n), 50, pair)
+        out[f"uni_0to1_{name}_GBps"] = round(n / (t / 50) / 1e9, 2)
+        events_around(lambda: bidir(n), 5, pair)
+        t = events_around(lambda: bidir(n), 50, pair)
+        out[f"bidir_0and1_{name}_GBps"] = round(2 * n / (t / 50) / 1e9, 2)
+
+    # all-pairs: every rank sends 64 MiB to each of the other ranks at once (BASELINE configs[3])
+    n = min(64 << 20, B // max(world - 1, 1))
+    n -= n % 256
+    def allpairs():
+        with p2p.group():
+            slot = 0
+            for p in range(world):
+                if p == rank:
+                    continue
+                p2p.recv(dst.ptr + slot * n, n, p2p.INT8, p, stream)
+                slot += 1
+            for p in range(world):
+                if p != rank:
+                    p2p.send(src.ptr, n, p2p.INT8, p, stream)
+    events_around(allpairs, 3)
+    t = events_around(allpairs, 30)
+    out["allpairs_bytes_per_flow"] = n
+    out["allpairs_aggregate_GBps"] = round(world * (world - 1) * n / (t / 30) / 1e9, 2)
+    p2p.raise_async_error()
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    return engine_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -103,6 +103,7 @@ struct Options {
     bool verify = false;
     bool extra = false;                 // print GB/s / us / % tables next to the Gbps ones
     bool first_pair_only = false;
+    bool e2e = false;                   // ring mode: host buffers, H2D + transfer + D2H inside the timed region
     size_t sweep_min = 8, sweep_max = 1ull << 30;
     std::string json;
     uint64_t seed = 0x5EED0000ull;
@@ -131,11 +132,12 @@ inline void usage(const char* prog, const char* backend) {
            "  --size BYTES[K|M|G]   message size (default 32M)\n"
            "  --iters N             timed iterations per cell (default 128)\n"
            "  --warmup N            untimed iterations per cell (default 0 for --timing ref, 20 for dev)\n"
-           "  --mode M              ref | uni | bidir | allpairs | sweep | latency | local\n"
+           "  --mode M              ref | uni | bidir | allpairs | ring | sweep | latency | local\n"
            "  --timing T            ref (rank-0 wall clock, sync per message) | dev (cudaEvents, back to back)\n"
            "  --verify              patterned payload, byte-exact check of every cell's receive buffer\n"
            "  --extra               also print GB/s, us per message and %% of 900 GB/s tables\n"
            "  --first-pair          only the pair 0 -> 1 instead of all ordered pairs\n"
+           "  --e2e                 (ring) payload starts and ends in pinned HOST memory: H2D + transfer + D2H per step\n"
            "  --sweep-min/--sweep-max BYTES   range of --mode sweep (default 8 .. 1G)\n"
            "  --json FILE           write every measurement as JSON lines\n"
            "  --seed N              pattern seed for --verify\n",
@@ -162,6 +164,7 @@ inline Options parse_args(int argc, char** argv, int rank, const char* backend) 
         else if (a == "--verify") o.verify = true;
         else if (a == "--extra") o.extra = true;
         else if (a == "--first-pair") o.first_pair_only = true;
+        else if (a == "--e2e") o.e2e = true;
         else if (a == "--sweep-min") ok = parse_size(need("--sweep-min"), &o.sweep_min);
         else if (a == "--sweep-max") ok = parse_size(need("--sweep-max"), &o.sweep_max);
         else if (a == "--json") o.json = need("--json");
@@ -281,9 +284,9 @@ public:
         }
         MPI_Barrier(MPI_COMM_WORLD);
         one_message(src, dst, bytes, bidir, true);
-        uint64_t bad = 0, digest = 0;
-        if (rank_ == dst) bad += be_.check(recv_, bytes, o_.seed, src, iter, s0_, &digest);
-        if (bidir && rank_ == src) bad += be_.check(recv_, bytes, o_.seed, dst, iter, s0_, &digest);
+        uint64_t bad = 0, digest = 0, digest_sum = 0;
+        if (rank_ == dst) { bad += be_.check(recv_, bytes, o_.seed, src, iter, s0_, &digest); digest_sum += digest; }
+        if (bidir && rank_ == src) { bad += be_.check(recv_, bytes, o_.seed, dst, iter, s0_, &digest); digest_sum += digest; }
         // the byte after the payload must still be poison (no overrun) when there is room
         if ((rank_ == dst || (bidir && rank_ == src)) && bytes < poison) {
             uint8_t guard[64] = {};
@@ -291,8 +294,18 @@ public:
             for (size_t i = 0; i < poison - bytes; ++i)
                 if (guard[i] != 0xA5) ++bad;
         }
-        unsigned long long b = bad, total = 0;
+        unsigned long long b = bad, total = 0, dg = digest_sum, dg_total = 0;
         MPICHECK(MPI_Allreduce(&b, &total, 1, MPI_UINT64_T, MPI_SUM, MPI_COMM_WORLD));
+        MPICHECK(MPI_Allreduce(&dg, &dg_total, 1, MPI_UINT64_T, MPI_SUM, MPI_COMM_WORLD));
+        if (json_) {
+            // digest of what the receiver(s) hold after the transfer (sum over both ends when bidir)
+            fprintf(json_,
+                    "{\"backend\": \"%s\", \"mode\": \"verify\", \"dir\": \"%s\", \"ranks\": %d, \"src\": %d, \"dst\": %d, "
+                    "\"bytes\": %zu, \"seed\": %llu, \"iter\": %llu, \"mismatches\": %llu, \"digest\": \"0x%016llx\"}\n",
+                    be_.name(), bidir ? "bidir" : "uni", size_, src, dst, bytes, (unsigned long long)o_.seed,
+                    (unsigned long long)iter, total, dg_total);
+            fflush(json_);
+        }
         verified_cells_++;
         verified_bytes_ += bytes * (bidir ? 2 : 1);
         verify_failures_ += total;
@@ -417,6 +430,72 @@ public:
             fflush(stdout);
         }
         record("allpairs", -1, -1, bytes, t, flows);
+    }
+
+    // ---- ring: every rank sends `bytes` to (rank+1)%N and receives from (rank-1)%N at once.
+    // N = 1 is a local copy through the same send/recv path.  This is bench.py's step.
+    void run_ring() {
+        const size_t bytes = o_.size;
+        const int right = (rank_ + 1) % size_, left = (rank_ + size_ - 1) % size_;
+        uint8_t *hsrc = nullptr, *hdst = nullptr;
+        if (o_.e2e) {
+            CUDACHECK(cudaMallocHost(&hsrc, bytes ? bytes : 1));
+            CUDACHECK(cudaMallocHost(&hdst, bytes ? bytes : 1));
+            memset(hsrc, 0x3c, bytes);
+        }
+        auto step = [&](bool sync) {
+            if (o_.e2e) CUDACHECK(cudaMemcpyAsync(send_, hsrc, bytes, cudaMemcpyHostToDevice, s0_));
+            be_.group_start();
+            be_.recv(recv_, bytes, left, s0_);
+            be_.send(send_, bytes, right, s0_);
+            be_.group_end();
+            if (o_.e2e) CUDACHECK(cudaMemcpyAsync(hdst, recv_, bytes, cudaMemcpyDeviceToHost, s0_));
+            if (sync) CUDACHECK(cudaStreamSynchronize(s0_));
+        };
+        if (o_.verify) {
+            be_.fill(send_, bytes, o_.seed, rank_, 4242, s0_);
+            CUDACHECK(cudaMemsetAsync(recv_, 0xA5, bytes, s0_));
+            CUDACHECK(cudaStreamSynchronize(s0_));
+            MPI_Barrier(MPI_COMM_WORLD);
+            const bool keep = o_.e2e;
+            o_.e2e = false;
+            step(true);
+            o_.e2e = keep;
+            uint64_t digest;
+            unsigned long long b = be_.check(recv_, bytes, o_.seed, left, 4242, s0_, &digest), total = 0;
+            MPICHECK(MPI_Allreduce(&b, &total, 1, MPI_UINT64_T, MPI_SUM, MPI_COMM_WORLD));
+            verified_cells_ += (uint64_t)size_;
+            verified_bytes_ += (uint64_t)size_ * bytes;
+            verify_failures_ += total;
+        }
+        for (int i = 0; i < std::max(o_.warmup, 3); ++i) step(true);
+        double t;
+        MPI_Barrier(MPI_COMM_WORLD);
+        if (o_.timing == "dev") {
+            CUDACHECK(cudaEventRecord(ev_[0], s0_));
+            for (int i = 0; i < o_.iters; ++i) step(false);
+            CUDACHECK(cudaEventRecord(ev_[1], s0_));
+            CUDACHECK(cudaStreamSynchronize(s0_));
+            float ms;
+            CUDACHECK(cudaEventElapsedTime(&ms, ev_[0], ev_[1]));
+            double mine = ms * 1e-3 / o_.iters;
+            MPICHECK(MPI_Allreduce(&mine, &t, 1, MPI_DOUBLE, MPI_MAX, MPI_COMM_WORLD));
+        } else {
+            auto start = std::chrono::system_clock::now();
+            for (int i = 0; i < o_.iters; ++i) step(true);
+            MPI_Barrier(MPI_COMM_WORLD);
+            std::chrono::duration<double> el = std::chrono::system_clock::now() - start;
+            t = el.count() / o_.iters;
+            MPICHECK(MPI_Bcast(&t, 1, MPI_DOUBLE, 0, MPI_COMM_WORLD));
+        }
+        const double agg = (double)size_ * bytes / t / 1e9;
+        if (rank_ == 0) {
+            printf("Ring%s (%s, timing %s): %d ranks, %zu bytes each to the next rank\n", o_.e2e ? " host-to-host" : "",
+                   be_.name(), o_.timing.c_str(), size_, bytes);
+            printf("  step %.2f us   aggregate %.2f GB/s   per GPU %.2f GB/s\n", t * 1e6, agg, agg / size_);
+            fflush(stdout);
+        }
+        record(o_.e2e ? "ring_e2e" : "ring", -1, -1, bytes, t, (double)size_);
     }
 
     // ---- size sweep on the pair 0 -> 1: streaming bandwidth and ping-pong latency per size
@@ -635,6 +714,7 @@ int run_main(Backend& be, int argc, char** argv) {
     else if (opt.mode == "uni") d.run_ref_tables(true, false);
     else if (opt.mode == "bidir") d.run_ref_tables(false, true);
     else if (opt.mode == "allpairs") d.run_allpairs();
+    else if (opt.mode == "ring") d.run_ring();
     else if (opt.mode == "sweep") d.run_sweep(false);
     else if (opt.mode == "latency") d.run_sweep(true);
     else if (opt.mode == "local") d.run_local();

@@ -1,0 +1,294 @@
+"""Parity tests on one B200: every data path of the engine, called through the C ABI
+(ctypes on libb200p2p.so), compared byte for byte with the oracle.
+
+One GPU means one rank, so the transfer is a self send/recv inside a group — the same fused
+kernel, flags, sequence rings and copy loops a peer transfer uses, with the "peer" mapping
+pointing at local memory.  Cross-GPU runs are in test_gpu_multi.py.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SEED = 0x5EED0000
+CAP = 64 << 20
+
+
+@pytest.fixture(scope="module")
+def eng(p2p, oracle):
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a GPU"
+    torch.cuda.set_device(0)
+    p2p.init(0, 1, 0)
+    src = p2p.DeviceBuffer(CAP + 4096)
+    dst = p2p.DeviceBuffer(CAP + 4096)
+    win = p2p.register(dst.ptr, dst.nbytes)
+    stream = torch.cuda.Stream()
+
+    class E:
+        pass
+
+    e = E()
+    e.p2p, e.oracle, e.src, e.dst, e.win, e.stream, e.torch = p2p, oracle, src, dst, win, stream, torch
+    e.iter = 0
+    yield e
+    p2p.set_option("path", p2p.PATH_AUTO)
+    torch.cuda.synchronize()
+    p2p.finalize()
+
+
+def transfer(e, n, src_off=0, dst_off=0, dtype=None, count=None):
+    """One patterned self transfer of n bytes; returns the received bytes plus 32 guard bytes either side."""
+    p2p, torch = e.p2p, e.torch
+    e.iter += 1
+    it = e.iter
+    p2p.pattern_fill(e.src.ptr + src_off, n, SEED, 0, it, e.stream)
+    e.dst.tensor().fill_(0xA5)
+    torch.cuda.synchronize()
+    dtype = p2p.INT8 if dtype is None else dtype
+    count = n if count is None else count
+    with p2p.group():
+        p2p.recv(e.dst.ptr + dst_off, count, dtype, 0, e.stream)
+        p2p.send(e.src.ptr + src_off, count, dtype, 0, e.stream)
+    e.stream.synchronize()
+    p2p.raise_async_error()
+    lo = max(0, dst_off - 32)
+    got = e.dst.tensor()[lo: dst_off + n + 32].cpu().numpy()
+    return got, dst_off - lo, it
+
+
+def assert_exact(e, n, src_off=0, dst_off=0, **kw):
+    got, lead, it = transfer(e, n, src_off, dst_off, **kw)
+    want = e.oracle.expected_recv(n, SEED, 0, it)
+    body = got[lead: lead + n]
+    if not np.array_equal(body, want):
+        diff = np.nonzero(body != want)[0]
+        raise AssertionError(f"{n} bytes (src+{src_off}, dst+{dst_off}): {diff.size} bytes differ, first at {diff[0]}")
+    assert np.all(got[:lead] == 0xA5), "wrote before the start of the receive buffer"
+    assert np.all(got[lead + n:] == 0xA5), "wrote past the end of the message"
+
+
+SIZES = [0, 1, 7, 8, 9, 15, 16, 17, 31, 32, 33, 255, 4095, 4096, 4097, 16383, 16384, 16385, 65535, 65536, 65537,
+         (1 << 20) - 1, 1 << 20, (1 << 20) + 3, (4 << 20) + 16, 16 << 20]
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_auto_path_sizes(eng, n):
+    eng.p2p.set_option("path", eng.p2p.PATH_AUTO)
+    assert_exact(eng, n)
+
+
+@pytest.mark.parametrize("vec", [16, 32])
+@pytest.mark.parametrize("n", [16385, 65536, (1 << 20) + 3, (8 << 20) + 48, 32 << 20])
+def test_ldst_path(eng, n, vec):
+    eng.p2p.set_option("path", eng.p2p.PATH_LDST)
+    eng.p2p.set_option("vec_bytes", vec)
+    try:
+        assert eng.p2p.query_plan(n, 0)[0] == eng.p2p.PATH_LDST
+        assert_exact(eng, n)
+    finally:
+        eng.p2p.set_option("vec_bytes", 16)
+
+
+@pytest.mark.parametrize("chunk,stages", [(16384, 8), (32768, 4), (8192, 16), (65536, 3)])
+@pytest.mark.parametrize("n", [16400, 65536, (1 << 20) + 3, (8 << 20) + 48, 32 << 20])
+def test_tma_path(eng, n, chunk, stages):
+    p2p = eng.p2p
+    p2p.set_option("path", p2p.PATH_TMA)
+    p2p.set_option("tma_stages", 2)
+    p2p.set_option("tma_chunk", chunk)
+    p2p.set_option("tma_stages", stages)
+    try:
+        assert p2p.query_plan(n, 0)[0] == p2p.PATH_TMA
+        assert_exact(eng, n)
+    finally:
+        p2p.set_option("tma_stages", 2)
+        p2p.set_option("tma_chunk", 16384)
+        p2p.set_option("tma_stages", 8)
+
+
+@pytest.mark.parametrize("path", ["ldst", "tma", "auto"])
+@pytest.mark.parametrize("src_off,dst_off", [(0, 0), (1, 1), (3, 19), (16, 48), (5, 6), (8, 0), (4, 0), (2, 0), (0, 1), (13, 7)])
+def test_misaligned_buffers(eng, path, src_off, dst_off):
+    """Same 16-byte phase, and every relative misalignment class (8, 4, 2, 1 bytes)."""
+    p2p = eng.p2p
+    p2p.set_option("path", {"ldst": p2p.PATH_LDST, "tma": p2p.PATH_TMA, "auto": p2p.PATH_AUTO}[path])
+    for n in (100, 70_001, (2 << 20) + 5):
+        assert_exact(eng, n, src_off, dst_off)
+
+
+@pytest.mark.parametrize("dtype_name,size", [("INT8", 1), ("UINT8", 1), ("INT32", 4), ("UINT32", 4), ("INT64", 8),
+                                              ("UINT64", 8), ("FLOAT16", 2), ("FLOAT32", 4), ("FLOAT64", 8),
+                                              ("BFLOAT16", 2), ("FLOAT8E4M3", 1), ("FLOAT8E5M2", 1)])
+def test_datatypes_scale_count(eng, dtype_name, size):
+    """dtype only scales count to bytes (ncclDataType_t numbering, nccl.h:278-291)."""
+    eng.p2p.set_option("path", eng.p2p.PATH_AUTO)
+    count = 100_003
+    assert_exact(eng, count * size, dtype=getattr(eng.p2p, dtype_name), count=count)
+
+
+def test_cfg1_shape_64mib_float(eng):
+    """BASELINE config 1's message: 16,777,216 float32 = 64 MiB."""
+    eng.p2p.set_option("path", eng.p2p.PATH_AUTO)
+    assert_exact(eng, 64 << 20, dtype=eng.p2p.FLOAT32, count=16_777_216)
+
+
+def test_sequence_rings_wrap(eng):
+    """More messages than ring slots on both protocols (64 rendezvous, 8 eager) without a host sync."""
+    p2p = eng.p2p
+    p2p.set_option("path", p2p.PATH_AUTO)
+    for n, reps in ((64, 40), (100_000, 150)):
+        p2p.pattern_fill(eng.src.ptr, n, SEED, 0, 9000 + n, eng.stream)
+        eng.dst.tensor().fill_(0xA5)
+        eng.torch.cuda.synchronize()
+        for _ in range(reps):
+            with p2p.group():
+                p2p.recv(eng.dst.ptr, n, p2p.INT8, 0, eng.stream)
+                p2p.send(eng.src.ptr, n, p2p.INT8, 0, eng.stream)
+        eng.stream.synchronize()
+        p2p.raise_async_error()
+        got = eng.dst.tensor()[:n].cpu().numpy()
+        assert np.array_equal(got, eng.oracle.expected_recv(n, SEED, 0, 9000 + n))
+
+
+def test_group_with_several_transfers(eng):
+    """Four sends and four receives of different sizes and protocols in one group (one launch)."""
+    p2p = eng.p2p
+    p2p.set_option("path", p2p.PATH_AUTO)
+    sizes = [8, 5000, 300_000, 3 << 20]
+    offs = [0, 1 << 20, 2 << 20, 8 << 20]
+    for k, (n, off) in enumerate(zip(sizes, offs)):
+        p2p.pattern_fill(eng.src.ptr + off, n, SEED, 0, 500 + k, eng.stream)
+    eng.dst.tensor().fill_(0xA5)
+    eng.torch.cuda.synchronize()
+    with p2p.group():
+        for n, off in zip(sizes, offs):
+            p2p.recv(eng.dst.ptr + off, n, p2p.INT8, 0, eng.stream)
+        for n, off in zip(sizes, offs):
+            p2p.send(eng.src.ptr + off, n, p2p.INT8, 0, eng.stream)
+    eng.stream.synchronize()
+    p2p.raise_async_error()
+    for k, (n, off) in enumerate(zip(sizes, offs)):
+        got = eng.dst.tensor()[off: off + n + 8].cpu().numpy()
+        assert np.array_equal(got[:n], eng.oracle.expected_recv(n, SEED, 0, 500 + k))
+        assert np.all(got[n:] == 0xA5)
+
+
+def test_two_streams_in_one_group(eng):
+    """The reference's bidirectional call shape: send on s_0, recv on s_1, grouped (p2p_matrix.cc:212-228)."""
+    p2p, torch = eng.p2p, eng.torch
+    s1 = torch.cuda.Stream()
+    n = (4 << 20) + 7
+    p2p.pattern_fill(eng.src.ptr, n, SEED, 0, 77, eng.stream)
+    eng.dst.tensor().fill_(0xA5)
+    torch.cuda.synchronize()
+    with p2p.group():
+        p2p.send(eng.src.ptr, n, p2p.INT8, 0, eng.stream)
+        p2p.recv(eng.dst.ptr, n, p2p.INT8, 0, s1)
+    s1.synchronize()   # completion must be visible on the receive stream alone
+    got = eng.dst.tensor()[:n].cpu().numpy()
+    eng.stream.synchronize()
+    assert np.array_equal(got, eng.oracle.expected_recv(n, SEED, 0, 77))
+
+
+def test_full_size_256mib_properties(eng, p2p, oracle):
+    """BASELINE's 256 MiB message: checked by size-independent properties — device-side byte
+    compare against the pattern, digest equal to the oracle's digest of the sender's payload,
+    and idempotence (a second transfer changes nothing)."""
+    import torch
+    n = 256 << 20
+    src = p2p.DeviceBuffer(n)
+    dst = p2p.DeviceBuffer(n + 64)
+    win = p2p.register(dst.ptr, dst.nbytes)
+    stream = torch.cuda.Stream()
+    try:
+        for path in (p2p.PATH_LDST, p2p.PATH_TMA):
+            p2p.set_option("path", path)
+            p2p.pattern_fill(src.ptr, n, SEED, 0, 1000 + path, stream)
+            dst.tensor().fill_(0xA5)
+            torch.cuda.synchronize()
+            for _ in range(2):
+                with p2p.group():
+                    p2p.recv(dst.ptr, n, p2p.INT8, 0, stream)
+                    p2p.send(src.ptr, n, p2p.INT8, 0, stream)
+                bad, first, dig = p2p.pattern_check(dst.ptr, n, SEED, 0, 1000 + path, stream)
+                assert bad == 0, f"path {path}: {bad} bytes differ, first at {first}"
+                assert dig == oracle.pattern_digest(n, SEED, 0, 1000 + path)
+                assert dig == p2p.digest(src.ptr, n, stream)
+            assert bytes(dst.tensor()[n: n + 64].cpu().numpy()) == b"\xa5" * 64
+            p2p.raise_async_error()
+    finally:
+        p2p.set_option("path", p2p.PATH_AUTO)
+        torch.cuda.synchronize()
+        p2p.deregister(win)
+        src.free()
+        dst.free()
+
+
+def test_unregistered_receive_buffer_is_refused(eng):
+    p2p = eng.p2p
+    other = p2p.DeviceBuffer(1 << 20)
+    try:
+        with pytest.raises(p2p.P2PError) as ei:
+            with p2p.group():
+                p2p.recv(other.ptr, 1 << 20, p2p.INT8, 0, eng.stream)
+                p2p.send(eng.src.ptr, 1 << 20, p2p.INT8, 0, eng.stream)
+        assert ei.value.code == p2p.INVALID_USAGE and "registered window" in str(ei.value)
+        # nothing was enqueued and no sequence number moved: the next transfer still matches
+        assert_exact(eng, 1 << 20)
+        # eager-sized messages need no window
+        it = 4321
+        p2p.pattern_fill(eng.src.ptr, 1000, SEED, 0, it, eng.stream)
+        with p2p.group():
+            p2p.recv(other.ptr, 1000, p2p.INT8, 0, eng.stream)
+            p2p.send(eng.src.ptr, 1000, p2p.INT8, 0, eng.stream)
+        eng.stream.synchronize()
+        assert np.array_equal(other.tensor()[:1000].cpu().numpy(), eng.oracle.expected_recv(1000, SEED, 0, it))
+    finally:
+        other.free()
+
+
+def test_argument_errors(eng):
+    p2p = eng.p2p
+    L = p2p.lib()
+    assert L.p2p_send(ctypes.c_void_p(eng.src.ptr), 8, 12, 0, None) == p2p.INVALID_ARGUMENT    # dtype out of range
+    assert L.p2p_send(ctypes.c_void_p(eng.src.ptr), 8, -1, 0, None) == p2p.INVALID_ARGUMENT
+    assert L.p2p_send(ctypes.c_void_p(eng.src.ptr), 8, 0, 1, None) == p2p.INVALID_ARGUMENT     # peer out of range
+    assert L.p2p_recv(ctypes.c_void_p(eng.dst.ptr), 8, 0, -1, None) == p2p.INVALID_ARGUMENT
+    assert L.p2p_send(None, 8, 0, 0, None) == p2p.INVALID_ARGUMENT                              # null buffer
+    assert L.p2p_send(ctypes.c_void_p(eng.src.ptr), 2**62, 8, 0, None) == p2p.INVALID_ARGUMENT  # overflow
+    assert L.p2p_group_end() == p2p.INVALID_USAGE                                               # unbalanced
+    assert L.p2p_init(0, 1, 0) == p2p.INVALID_USAGE                                             # twice
+    assert L.p2p_set_option(b"nonsense", 1) == p2p.INVALID_ARGUMENT
+    assert L.p2p_set_option(b"vec_bytes", 24) == p2p.INVALID_ARGUMENT
+    assert p2p.async_error() == p2p.SUCCESS
+    assert_exact(eng, 4096)
+
+
+def test_missing_peer_times_out_instead_of_hanging(eng):
+    """A receive whose sender never comes reports P2P_REMOTE_ERROR after the timeout.  Run in a
+    process of its own: the unmatched receive leaves that engine's sequence numbers unusable."""
+    from conftest import ROOT, run
+    code = r'''
+import importlib, sys
+sys.path.insert(0, %r)
+import torch
+p2p = importlib.import_module("test-nccl-p2p_b200")
+torch.cuda.set_device(0)
+p2p.init(0, 1, 0)
+buf = p2p.DeviceBuffer(1 << 20)
+p2p.register(buf.ptr, buf.nbytes)
+p2p.set_option("timeout_ms", 200)
+s = torch.cuda.Stream()
+p2p.recv(buf.ptr, 1 << 20, p2p.INT8, 0, s)      # rendezvous receive, no matching send
+s.synchronize()
+assert p2p.async_error() == p2p.REMOTE_ERROR
+assert "never completed" in p2p.lib().p2p_get_last_error().decode()
+p2p.recv(buf.ptr, 64, p2p.INT8, 0, s)           # eager receive, no matching send
+s.synchronize()
+assert p2p.async_error() == p2p.REMOTE_ERROR
+print("timed out cleanly")
+''' % ROOT
+    assert "timed out cleanly" in run(["python", "-c", code], timeout=120).stdout
