@@ -164,6 +164,25 @@ P2P_API int p2p_pattern_check(const void* buf, size_t bytes, uint64_t seed, int 
 /* 64-bit order-dependent digest of any device buffer (same function as above). */
 P2P_API int p2p_digest(const void* buf, size_t bytes, p2p_stream_t stream, uint64_t* digest);
 
+/* ---- no counterpart in the reference: p2p_digest for callers that may not allocate.
+ *      Who that is: a process whose framework already owns all of HBM (a cudaMalloc from a
+ *      library would fail or fragment its pool), a loop that cannot afford the device-wide
+ *      synchronisation cudaMalloc/cudaFree imply, or a checker that runs without p2p_init.
+ *      The scratch the digest kernel needs (per-CTA partial sums, an arrival ticket, the
+ *      result) lives in a fixed array inside the library's device image, so this call — unlike
+ *      every other entry point — needs no p2p_init and performs no allocation of any kind.
+ *      Limits and rules:
+ *        - bytes <= P2P_NOALLOC_MAX_BYTES (the array holds 4096 partial sums, one per 256 KiB
+ *          of input); larger buffers are refused with P2P_INVALID_ARGUMENT;
+ *        - `digest_dev` is DEVICE memory (8 bytes) the caller owns; the call is asynchronous
+ *          on `stream`, the value is there once the stream has caught up;
+ *        - the first call on each device looks up that device's copy of the array; make that
+ *          first call with the device current and outside any stream capture;
+ *        - all calls on a device share the one array: two calls whose kernels could overlap
+ *          (different streams, no dependency) race and give garbage — serialise them. ---- */
+#define P2P_NOALLOC_MAX_BYTES (1ull << 30)
+P2P_API int p2p_digest_noalloc(const void* buf, size_t bytes, p2p_stream_t stream, uint64_t* digest_dev);
+
 #ifdef __cplusplus
 }
 #endif

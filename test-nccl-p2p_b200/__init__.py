@@ -35,8 +35,9 @@ SYMBOLS = [
     "p2p_register_blob_bytes", "p2p_register_export", "p2p_register_import", "p2p_deregister",
     "p2p_mem_alloc", "p2p_mem_free", "p2p_send", "p2p_recv", "p2p_group_start", "p2p_group_end",
     "p2p_get_error_string", "p2p_get_last_error", "p2p_get_async_error", "p2p_set_option", "p2p_get_option",
-    "p2p_query_plan", "p2p_pattern_fill", "p2p_pattern_check", "p2p_digest",
+    "p2p_query_plan", "p2p_pattern_fill", "p2p_pattern_check", "p2p_digest", "p2p_digest_noalloc",
 ]
+NOALLOC_MAX_BYTES = 1 << 30
 
 
 class P2PError(RuntimeError):
@@ -87,6 +88,7 @@ def lib() -> ctypes.CDLL:
         "p2p_pattern_fill": (i32, [vp, sz, u64, i32, u64, vp]),
         "p2p_pattern_check": (i32, [vp, sz, u64, i32, u64, vp, pu64, pu64, pu64]),
         "p2p_digest": (i32, [vp, sz, vp, pu64]),
+        "p2p_digest_noalloc": (i32, [vp, sz, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -267,3 +269,8 @@ def digest(ptr: int, nbytes: int, stream=None) -> int:
     dig = ctypes.c_uint64(0)
     check(lib().p2p_digest(ctypes.c_void_p(ptr), nbytes, _stream_ptr(stream), ctypes.byref(dig)))
     return dig.value
+
+
+def digest_noalloc(ptr: int, nbytes: int, out_dev_ptr: int, stream=None) -> None:
+    """p2p_digest_noalloc: asynchronous, result (8 bytes) lands in device memory at out_dev_ptr."""
+    check(lib().p2p_digest_noalloc(ctypes.c_void_p(ptr), nbytes, _stream_ptr(stream), ctypes.c_void_p(out_dev_ptr)))

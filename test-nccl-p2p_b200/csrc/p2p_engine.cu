@@ -135,6 +135,18 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 
+}  // namespace
+
+int set_last_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_last_error, sizeof t_last_error, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+namespace {
+
 #define CUDA_TRY(expr)                                                                          \
     do {                                                                                        \
         cudaError_t e_ = (expr);                                                                \

@@ -42,6 +42,9 @@ struct CheckPartial {
     uint64_t digest;
 };
 
+// records the text p2p_get_last_error() returns (this thread) and hands `code` back
+int set_last_error(int code, const char* fmt, ...);
+
 cudaError_t configure_kernels(int max_tma_smem);
 cudaError_t occupancy(int flavour, int dyn_smem, int* ctas_per_sm);
 cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, int dyn_smem, cudaStream_t stream);

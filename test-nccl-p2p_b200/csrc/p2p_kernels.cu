@@ -1,4 +1,5 @@
 // Kernels of the transfer engine and their launch wrappers (compiled for sm_100a only).
+#include "p2p.h"
 #include "p2p_internal.h"
 #include "p2p_tma.cuh"
 
@@ -220,4 +221,72 @@ cudaError_t launch_pattern_check(const void* buf, size_t nbytes, uint64_t key, i
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ digest without allocation
+//
+// p2p_digest() keeps its per-CTA partial sums, its arrival ticket and its result in device
+// memory that p2p_init() obtained with cudaMalloc.  Some callers of this library cannot have
+// that: a serving process whose framework has already claimed every byte of HBM for its own
+// pool (a late cudaMalloc simply fails there), a latency-critical loop that must not hit the
+// implicit device-wide synchronisation of cudaMalloc/cudaFree, or a tool that wants to check a
+// buffer without bringing the engine up at all.  For them the same kernel runs here against a
+// scratch area that is part of the loaded module itself: it exists on every GPU that loads the
+// library, from load until the process exits, and nobody has to ask for it.
+
+constexpr size_t kNoAllocSpan = 256 * 1024;       // input bytes covered per CTA (one partial each)
+constexpr unsigned kNoAllocMaxCtas = 4096;        // => P2P_NOALLOC_MAX_BYTES = 4096 * 256 KiB = 1 GiB
+static_assert((unsigned long long)kNoAllocMaxCtas * kNoAllocSpan == P2P_NOALLOC_MAX_BYTES, "header and kernel disagree");
+
+struct NoAllocScratch {
+    CheckPartial partials[kNoAllocMaxCtas];
+    CheckPartial out;
+    unsigned int ticket;
+};
+
+// 96 KiB and change.  In host code this name is only a stand-in for the symbol; the address a
+// kernel can use comes from cudaGetSymbolAddress, once per device (noalloc_scratch_for_device).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[(sizeof(NoAllocScratch) + 255) / 256 * 256];
+
 }  // namespace p2p
+
+namespace {
+constexpr int kMaxDevices = 64;
+p2p::NoAllocScratch* g_noalloc_ptr[kMaxDevices];  // per device, filled on first use
+}
+
+extern "C" int p2p_digest_noalloc(const void* buf, size_t bytes, p2p_stream_t stream, uint64_t* digest_dev) {
+    using namespace p2p;
+    if (!digest_dev) return set_last_error(P2P_INVALID_ARGUMENT, "p2p_digest_noalloc: null result pointer");
+    if (bytes && !buf) return set_last_error(P2P_INVALID_ARGUMENT, "p2p_digest_noalloc: null buffer");
+    if (bytes > P2P_NOALLOC_MAX_BYTES)
+        return set_last_error(P2P_INVALID_ARGUMENT,
+                              "p2p_digest_noalloc: %zu bytes exceed the %llu-byte limit of the built-in scratch area "
+                              "(%u partial sums, one per %zu input bytes); use p2p_digest for larger buffers",
+                              bytes, (unsigned long long)P2P_NOALLOC_MAX_BYTES, kNoAllocMaxCtas, kNoAllocSpan);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices)
+        return set_last_error(P2P_UNHANDLED_CUDA_ERROR, "p2p_digest_noalloc: no usable current device (%s)", cudaGetErrorString(e));
+    NoAllocScratch* scratch = g_noalloc_ptr[dev];
+    if (!scratch) {
+        // first call on this device: resolve the symbol to this device's copy of the array
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return set_last_error(P2P_UNHANDLED_CUDA_ERROR, "p2p_digest_noalloc: cudaGetSymbolAddress failed on device %d: %s",
+                                  dev, cudaGetErrorString(e));
+        scratch = (NoAllocScratch*)p;
+        g_noalloc_ptr[dev] = scratch;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    // the array still holds whatever the previous call left: the ticket must start from zero
+    e = cudaMemsetAsync(&scratch->ticket, 0, sizeof(unsigned int), s);
+    if (e != cudaSuccess) return set_last_error(P2P_UNHANDLED_CUDA_ERROR, "p2p_digest_noalloc: cudaMemsetAsync: %s", cudaGetErrorString(e));
+    unsigned ctas = (unsigned)((bytes + kNoAllocSpan - 1) / kNoAllocSpan);
+    if (ctas < 1) ctas = 1;
+    pattern_check_kernel<<<ctas, kPatThreads, 0, s>>>((const uint8_t*)buf, bytes, 0, 0, scratch->partials, &scratch->ticket, &scratch->out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return set_last_error(P2P_UNHANDLED_CUDA_ERROR, "p2p_digest_noalloc: launch failed: %s", cudaGetErrorString(e));
+    e = cudaMemcpyAsync(digest_dev, &scratch->out.digest, sizeof(uint64_t), cudaMemcpyDeviceToDevice, s);
+    if (e != cudaSuccess) return set_last_error(P2P_UNHANDLED_CUDA_ERROR, "p2p_digest_noalloc: result copy: %s", cudaGetErrorString(e));
+    return P2P_SUCCESS;
+}
