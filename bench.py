@@ -245,6 +245,7 @@ def engine_arm(args):
     p2p.init(rank, world, local, gather)
     src, dst = p2p.DeviceBuffer(B), p2p.DeviceBuffer(B + 256)
     p2p.register(dst.ptr, dst.nbytes, gather)
+    p2p.register(src.ptr, src.nbytes, gather)   # large messages may then be pulled by the receiver
     stream = torch.cuda.Stream()
     clocks = Clocks(local)
 
@@ -343,7 +344,8 @@ def engine_arm(args):
             "config": {"workload": f"ring step, {B} bytes per GPU (BASELINE configs[1] message size)"
                                    + ("; N=1: local HBM copy through the same send/recv kernel" if world == 1 else ""),
                        "bytes": B, "l2": "message larger than L2 (126 MB), no flush needed" if B > (126 << 20) else "message fits L2",
-                       "path": {1: "ldst", 2: "tma", 4: "eager"}.get(plan[0], str(plan[0])), "ctas": plan[1]},
+                       "path": ("local copy, " if world == 1 else "") + {1: "push ld/st", 2: "push tma", 4: "eager", 5: "pull ld/st"}.get(plan[0], str(plan[0])),
+                       "ctas": plan[1]},
             "clocks": clocks.summary(),
             "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": B * world, "d2h_bytes_per_step": B * world,
                     "steps": e2e_steps, "payload_intact": e2e_ok},

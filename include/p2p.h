@@ -18,10 +18,13 @@
  *     <allgather the blobs in rank order>
  *     p2p_connect(all_blobs);
  *
- * Receive buffers of messages larger than the eager limit must lie inside a registered
- * window (p2p_register_export / p2p_register_import, same two-phase shape), because the
- * sender's kernel stores straight into them through a peer mapping: one NVLink crossing,
- * no staging copy.  Send buffers need no registration.
+ * Payload crosses NVLink exactly once, straight between the two user buffers, through a peer
+ * mapping of a registered window (p2p_register_export / p2p_register_import, same two-phase
+ * shape): messages up to the eager limit need no window; above it the sender's kernel stores
+ * into the receiver's registered buffer (push); from the pull threshold up the receiver's
+ * kernel loads from the sender's registered buffer instead when it is registered (pull, the
+ * faster direction on B200), else the sender pushes.  Registering both buffers gives the
+ * engine the choice; at least the receive buffer must be registered below the pull threshold.
  *
  * Matching rules are NCCL's (nccl.h:438-462): the k-th p2p_send(count, dtype, peer=B) on
  * rank A pairs with the k-th p2p_recv(count, dtype, peer=A) on rank B, byte counts must
@@ -84,7 +87,7 @@ typedef enum {
 } p2p_datatype_t;
 
 #define P2P_MAX_RANKS 16      /* one NVSwitch domain on one host */
-#define P2P_MAX_WINDOWS 256   /* registered windows per rank */
+#define P2P_MAX_WINDOWS 255   /* registered windows per rank */
 #define P2P_MAX_GROUP_OPS 32  /* sends + recvs in one group */
 
 /* ---- lifecycle: replaces ncclGetUniqueId + MPI_Bcast + ncclCommInitRank
@@ -140,14 +143,17 @@ P2P_API const char* p2p_get_last_error(void);
 P2P_API int p2p_get_async_error(int* result);
 
 /* ---- tuning knobs (the reference has none; NCCL reads NCCL_* environment variables).
- *      Names: "path" (0 auto, 1 ldst, 2 tma, 3 ce), "nblocks" (CTAs per send, 0 auto),
- *      "eager_bytes" (LL limit; must match on all ranks, set before p2p_export),
- *      "timeout_ms" (device spin timeout), "unroll". Environment: P2P_PATH, P2P_NBLOCKS,
- *      P2P_EAGER_BYTES, P2P_TIMEOUT_MS read once in p2p_init. ---- */
+ *      Names: "path" (0 auto, 1 push with ld/st, 2 push with TMA), "nblocks" (CTAs per push, 0 auto),
+ *      "pull_nblocks", "self_nblocks", "eager_bytes" and "pull_min_bytes" (protocol limits; must match
+ *      on all ranks: environment only, read in p2p_init), "timeout_ms" (device spin timeout),
+ *      "tma_chunk", "tma_stages", "tma_min_bytes", "pdl" (programmatic dependent launch),
+ *      "loopback" (send-to-self goes through the wire protocol; for tests).  Environment:
+ *      P2P_PATH, P2P_NBLOCKS, P2P_PULL_NBLOCKS, P2P_SELF_NBLOCKS, P2P_EAGER_BYTES, P2P_PULL_MIN_BYTES,
+ *      P2P_TIMEOUT_MS, P2P_TMA_CHUNK, P2P_TMA_STAGES, P2P_TMA_MIN_BYTES, P2P_PDL, P2P_LOOPBACK. ---- */
 P2P_API int p2p_set_option(const char* name, long long value);
 P2P_API int p2p_get_option(const char* name, long long* value);
 /* What the selector would do for a message of `bytes` to `peer`: writes the path id
- * (1 ldst, 2 tma, 3 ce, 4 eager) and CTA count. */
+ * (1 push ld/st, 2 push TMA, 4 eager, 5 pull when the send buffer is registered) and CTA count. */
 P2P_API int p2p_query_plan(size_t bytes, int peer, int* path, int* nblocks);
 
 /* ---- verification support: the reference sends zeros and never reads recv_buff

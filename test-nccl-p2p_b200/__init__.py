@@ -27,7 +27,7 @@ DTYPE_SIZE = {INT8: 1, UINT8: 1, INT32: 4, UINT32: 4, INT64: 8, UINT64: 8, FLOAT
 
 SUCCESS, UNHANDLED_CUDA_ERROR, SYSTEM_ERROR, INTERNAL_ERROR, INVALID_ARGUMENT, INVALID_USAGE, REMOTE_ERROR, IN_PROGRESS = range(8)
 
-PATH_AUTO, PATH_LDST, PATH_TMA, PATH_CE, PATH_EAGER = 0, 1, 2, 3, 4
+PATH_AUTO, PATH_LDST, PATH_TMA, PATH_CE, PATH_EAGER, PATH_PULL = 0, 1, 2, 3, 4, 5
 
 # every symbol include/p2p.h declares; tests check the library exports exactly these
 SYMBOLS = [

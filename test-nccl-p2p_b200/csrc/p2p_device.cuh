@@ -6,12 +6,17 @@
 // range; the first CTA is the control CTA that posts and completes rendezvous receives.
 //
 // Protocols
-//   rendezvous  receiver posts {seq, window, offset} into the SENDER's control region;
-//               sender CTAs push payload straight into the receiver's buffer through the
+//   push        receiver posts {seq, window, offset} into the SENDER's control region;
+//               sender CTAs store payload straight into the receiver's buffer through the
 //               peer mapping, then the last CTA to finish publishes `done[seq]` in the
 //               RECEIVER's control region with a system-scope release store.
+//   pull        (large messages) the mirror image: sender posts where its payload lies,
+//               receiver CTAs LOAD it through the peer mapping (NVLink reads run ~8% faster
+//               than SM-issued writes on B200) and publish `pull_done[seq]` at the sender.
+//               The sender decides; a receiver of a large message adapts to what it is told.
 //   eager (LL)  8 payload bytes + two 4-byte flags per 16-byte store into a ring in the
 //               receiver's control region; the receiver copies out as flags turn valid.
+//   copy        send and receive of one rank to itself, matched on the host: a plain copy.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -19,7 +24,7 @@
 namespace p2p {
 
 constexpr int kRing = 64;            // outstanding rendezvous messages per ordered pair
-constexpr int kLLSlots = 8;          // eager ring depth per ordered pair
+constexpr int kLLSlots = 4;          // eager ring depth per ordered pair
 constexpr int kLdstThreads = 512;
 constexpr int kTmaThreads = 128;
 constexpr int kMaxGroupOps = 32;
@@ -27,41 +32,54 @@ constexpr int kTmaMaxStages = 16;
 
 enum OpKind : uint32_t {
     OP_NONE = 0,
-    OP_RECV_RDV = 1,   // handled by one thread of the control CTA
-    OP_SEND_RDV = 2,   // push payload (ld/st or TMA, by kernel flavour)
+    OP_POST = 1,        // one thread of the control CTA: publish `word`, wait for `f_wait == seq`
+    OP_PUSH = 2,        // mover CTAs: wait for the receiver's post, store local -> peer, signal done
     OP_SEND_LL = 3,
     OP_RECV_LL = 4,
+    OP_COPY = 5,        // mover CTAs: local -> local, no flags
+    OP_RECV_ADAPT = 6,  // mover CTAs: wait for the sender's word; pull peer -> local, or fall back to posting
 };
 
 enum AsyncError : uint32_t { AERR_NONE = 0, AERR_TIMEOUT_POST = 1, AERR_TIMEOUT_DONE = 2,
                              AERR_TIMEOUT_LL_DATA = 3, AERR_TIMEOUT_LL_ACK = 4, AERR_BAD_WINDOW = 5 };
 
-struct alignas(16) OpDesc {
-    uint64_t local;        // send: source pointer; recv: destination pointer (this GPU)
+struct alignas(8) OpDesc {
+    uint64_t local;      // this GPU's buffer: source of a send, destination of a receive
     uint64_t nbytes;
-    uint64_t wait_flag;    // local flag this op polls (send: post slot, recv: done slot, LL send: ack slot)
-    uint64_t signal_flag;  // peer-mapped flag this op writes (send: done, recv: post, LL recv: ack)
-    uint64_t word;         // recv: the post word; others unused
-    uint64_t seq;          // sequence number of this message on its (src,dst,protocol) lane
-    uint64_t aux;          // send: table of the peer's window bases; LL: ring slot (peer-mapped for send)
-    uint64_t arrive;       // send: local u32 arrival counter
+    uint64_t seq;        // sequence number of this message on its (src, dst, protocol) lane
+    uint64_t f_wait;     // local flag polled      (post: done slot; push: post slot; LL send: ack slot)
+    uint64_t f_signal;   // peer-mapped flag written (post: peer's post slot; push: done slot; LL recv: ack slot)
+    uint64_t word;       // post: the word to publish; adaptive receive: its own push post word (0: buffer not registered)
+    uint64_t f_wait2;    // adaptive receive: local slot the sender's word arrives in
+    uint64_t f_signal2;  // adaptive receive: sender's pull_done slot; push with notice: receiver's pull_post slot
+    uint64_t word2;      // push with notice: the "I will push" word
+    uint64_t aux;        // window table of the peer / LL ring slot / destination of a local copy
+    uint64_t arrive;     // local u32 arrival counter of the mover CTAs
     uint32_t kind;
     uint32_t first_block;
     uint32_t nblocks;
     uint32_t peer;
 };
 
-struct GroupArgs {
+struct GroupHdr {
     uint32_t nops;
-    uint32_t n_ctrl;         // rendezvous receives served by the control CTA (block 0) or 0
-    uint32_t vec_bytes;      // 16 or 32: ld/st width of the push loop
+    uint32_t n_ctrl;         // OP_POST ops served by the control CTA (block 0), or 0: no control CTA
+    uint32_t reserved;
     uint32_t tma_chunk;      // bytes per cp.async.bulk (TMA flavour)
     uint32_t tma_stages;
-    uint32_t pad;
+    uint32_t pdl;            // launched with programmatic stream serialisation
     uint64_t timeout_ns;
     uint32_t* async_err;     // host-mapped word; first error wins
-    OpDesc ops[kMaxGroupOps];
 };
+
+template <int MAXOPS>
+struct GroupArgsT {
+    GroupHdr h;
+    OpDesc ops[MAXOPS];
+};
+using GroupArgs = GroupArgsT<kMaxGroupOps>;
+constexpr int kSmallGroupOps = 4;
+using GroupArgsSmall = GroupArgsT<kSmallGroupOps>;
 
 // ---------------------------------------------------------------- PTX helpers
 
@@ -78,6 +96,9 @@ __device__ __forceinline__ uint64_t ld_relaxed_sys(const uint64_t* p) {
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void st_relaxed_sys(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ uint64_t globaltimer_ns() {
     uint64_t t;
@@ -85,7 +106,8 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
     return t;
 }
 
-// streaming 16- and 32-byte accesses: no L1 allocation, the payload is touched once
+// streaming 16-byte accesses: no L1 allocation, the payload is touched once.  (32-byte
+// LDG/STG.256 were measured too: same NVLink and HBM rates, twice the registers.)
 __device__ __forceinline__ uint4 ld_stream16(const void* p) {
     uint4 v;
     asm volatile("ld.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
@@ -96,20 +118,6 @@ __device__ __forceinline__ void st_stream16(void* p, const uint4& v) {
     asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1,%2,%3,%4};"
                  ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
-struct alignas(32) vec32 { uint32_t r[8]; };
-__device__ __forceinline__ vec32 ld_stream32(const void* p) {
-    vec32 v;
-    asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(v.r[0]), "=r"(v.r[1]), "=r"(v.r[2]), "=r"(v.r[3]),
-                   "=r"(v.r[4]), "=r"(v.r[5]), "=r"(v.r[6]), "=r"(v.r[7]) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_stream32(void* p, const vec32& v) {
-    asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
-                 ::"l"(p), "r"(v.r[0]), "r"(v.r[1]), "r"(v.r[2]), "r"(v.r[3]),
-                   "r"(v.r[4]), "r"(v.r[5]), "r"(v.r[6]), "r"(v.r[7]) : "memory");
-}
-
 // LL line: {data_lo, flag, data_hi, flag}; each 8-byte half is written atomically
 __device__ __forceinline__ void st_ll_line(void* p, uint64_t data, uint32_t flag) {
     asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};"
@@ -123,8 +131,18 @@ __device__ __forceinline__ uint4 ld_ll_line(const void* p) {
     return v;
 }
 
-__device__ __forceinline__ void report_error(const GroupArgs& a, uint32_t code) {
-    if (a.async_err) atomicCAS_system(a.async_err, 0u, code);
+__device__ __forceinline__ void report_error(const GroupHdr& h, uint32_t code) {
+    if (h.async_err) atomicCAS_system(h.async_err, 0u, code);
+}
+
+// Programmatic dependent launch: let the next kernel of the stream get resident while this one
+// runs, and hold this one until everything before it in the stream has completed.  Nothing that
+// depends on earlier stream work (user buffers, flags of earlier messages) is touched before.
+__device__ __forceinline__ void pdl_prologue(const GroupHdr& h) {
+    if (h.pdl) {
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
 }
 
 // Poll helper.  `pred(value)` decides; returns false on timeout.
@@ -149,20 +167,24 @@ __device__ __forceinline__ bool spin_flag(const uint64_t* flag, uint64_t timeout
 
 // Vectors [0, nvec) of width sizeof(V); this CTA is `part` of `nparts`.  Tiles of
 // blockDim.x*UNROLL vectors are dealt round-robin so that concurrently running CTAs
-// stream neighbouring addresses (DRAM pages and NVLink packets stay dense).
+// stream neighbouring addresses (DRAM pages and NVLink packets stay dense).  Inside a tile
+// each warp owns 32*UNROLL consecutive vectors and walks them in UNROLL coalesced steps of
+// 32 vectors, so the per-step offsets are immediates and one address register pair serves
+// all loads and one all stores.
 template <typename V, int UNROLL, typename LD, typename ST>
 __device__ __forceinline__ void copy_vectors(V* __restrict__ dst, const V* __restrict__ src,
                                              size_t nvec, uint32_t part, uint32_t nparts, LD ld, ST st) {
     const size_t tile = (size_t)blockDim.x * UNROLL;
     const size_t ntiles = nvec / tile;
+    const size_t in_tile = (size_t)(threadIdx.x >> 5) * (32 * UNROLL) + (threadIdx.x & 31);
     for (size_t t = part; t < ntiles; t += nparts) {
-        const V* s = src + t * tile + threadIdx.x;
-        V* d = dst + t * tile + threadIdx.x;
+        const V* s = src + t * tile + in_tile;
+        V* d = dst + t * tile + in_tile;
         V v[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) v[u] = ld(s + (size_t)u * blockDim.x);
+        for (int u = 0; u < UNROLL; ++u) v[u] = ld(s + u * 32);
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) st(d + (size_t)u * blockDim.x, v[u]);
+        for (int u = 0; u < UNROLL; ++u) st(d + u * 32, v[u]);
     }
     if (part == (uint32_t)(ntiles % nparts)) {
         for (size_t i = ntiles * tile + threadIdx.x; i < nvec; i += blockDim.x) st(dst + i, ld(src + i));
@@ -178,33 +200,26 @@ __device__ __forceinline__ void copy_elems(T* __restrict__ dst, const T* __restr
     for (; i < n; i += stride) dst[i] = src[i];
 }
 
-// Byte-exact copy of n bytes for arbitrary alignment of either side.
+struct Ld16 { __device__ __forceinline__ uint4 operator()(const uint4* p) const { return ld_stream16(p); } };
+struct St16 { __device__ __forceinline__ void operator()(uint4* p, const uint4& v) const { st_stream16(p, v); } };
+
+// Byte-exact copy of n bytes for arbitrary alignment of either side.  Each kernel
+// inlines it exactly once (see resolve_role), which keeps the hot loop free of spills.
 __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, size_t n, uint32_t part,
-                                           uint32_t nparts, uint32_t vec_bytes) {
+                                           uint32_t nparts) {
     if (n == 0) return;
     const uint64_t rel = ((uint64_t)dst ^ (uint64_t)src);
     if ((rel & 15) == 0) {
-        // same phase: byte head up to a 32-byte boundary, wide body, byte tail
-        size_t head = (32 - ((uint64_t)dst & 31)) & 31;
-        if ((rel & 31) != 0 || vec_bytes != 32) head = (16 - ((uint64_t)dst & 15)) & 15;
+        // same phase: byte head up to a 16-byte boundary, 16-byte body, byte tail
+        size_t head = (16 - ((uint64_t)dst & 15)) & 15;
         if (head > n) head = n;
         if (part == 0)
             for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = src[i];
         uint8_t* d = dst + head;
         const uint8_t* s = src + head;
-        size_t left = n - head;
-        size_t body;
-        if ((rel & 31) == 0 && vec_bytes == 32) {
-            body = left & ~(size_t)31;
-            copy_vectors<vec32, 4>((vec32*)d, (const vec32*)s, body / 32, part, nparts,
-                                   [](const vec32* p) { return ld_stream32(p); },
-                                   [](vec32* p, const vec32& v) { st_stream32(p, v); });
-        } else {
-            body = left & ~(size_t)15;
-            copy_vectors<uint4, 8>((uint4*)d, (const uint4*)s, body / 16, part, nparts,
-                                   [](const uint4* p) { return ld_stream16(p); },
-                                   [](uint4* p, const uint4& v) { st_stream16(p, v); });
-        }
+        const size_t left = n - head;
+        const size_t body = left & ~(size_t)15;
+        copy_vectors<uint4, 8>((uint4*)d, (const uint4*)s, body / 16, part, nparts, Ld16{}, St16{});
         if (part == nparts - 1)
             for (size_t i = body + threadIdx.x; i < left; i += blockDim.x) d[i] = s[i];
         return;
@@ -233,35 +248,41 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, siz
 
 // Post word layout: [63:48] low 16 bits of seq, [47:40] window id, [39] valid (always 1, so
 // a real post is never the all-zero word of a fresh slot), [38:0] byte offset (512 GiB).
+// Window id 0xFF in a SENDER's word means "I will push, post me your buffer".
 constexpr uint64_t kPostValid = 1ull << 39;
 constexpr uint64_t kPostOffMask = kPostValid - 1;
+constexpr uint32_t kWinPushPlease = 0xFFu;
 __host__ __device__ __forceinline__ uint64_t make_post_word(uint64_t seq, uint32_t win, uint64_t off) {
     return ((seq & 0xffffull) << 48) | ((uint64_t)(win & 0xffu) << 40) | kPostValid | (off & kPostOffMask);
 }
 
-// One thread per rendezvous receive: publish where the payload goes, then wait for it.
-__device__ __forceinline__ void ctrl_recv(const GroupArgs& a, const OpDesc& op) {
-    st_release_sys((uint64_t*)op.signal_flag, op.word);
+// One control thread: publish a post word, then wait for the matching completion flag.
+__device__ __forceinline__ void post_and_wait(const GroupHdr& h, const OpDesc& op) {
+    st_release_sys((uint64_t*)op.f_signal, op.word);
     uint64_t v;
     const uint64_t want = op.seq;
-    if (!spin_flag((const uint64_t*)op.wait_flag, a.timeout_ns, v, [want](uint64_t x) { return x == want; }))
-        report_error(a, AERR_TIMEOUT_DONE);
+    if (!spin_flag((const uint64_t*)op.f_wait, h.timeout_ns, v, [want](uint64_t x) { return x == want; }))
+        report_error(h, AERR_TIMEOUT_DONE);
 }
 
-// All CTAs of a send learn the destination; returns nullptr on timeout / bad window.
-__device__ __forceinline__ uint8_t* send_wait_post(const GroupArgs& a, const OpDesc& op, uint64_t* smem_slot) {
+// Thread 0 waits for the word tagged with this message's sequence number in `slot`.
+__device__ __forceinline__ bool wait_word(const GroupHdr& h, const uint64_t* slot, uint64_t seq, uint64_t& word) {
+    const uint64_t tag = seq & 0xffffull;
+    return spin_flag(slot, h.timeout_ns, word, [tag](uint64_t x) { return (x >> 48) == tag && (x & kPostValid); });
+}
+
+// All CTAs of a push learn the destination; returns nullptr on timeout / bad window.
+__device__ __forceinline__ uint8_t* push_wait_post(const GroupHdr& h, const OpDesc& op, uint32_t part, uint64_t* smem_slot) {
     if (threadIdx.x == 0) {
-        uint64_t v = 0;
-        const uint64_t tag = op.seq & 0xffffull;
-        uint64_t dst = 0;
-        if (spin_flag((const uint64_t*)op.wait_flag, a.timeout_ns, v,
-                      [tag](uint64_t x) { return (x >> 48) == tag && (x & kPostValid); })) {
+        if (part == 0 && op.f_signal2) st_release_sys((uint64_t*)op.f_signal2, op.word2);  // "I will push"
+        uint64_t v = 0, dst = 0;
+        if (wait_word(h, (const uint64_t*)op.f_wait, op.seq, v)) {
             const uint32_t win = (uint32_t)(v >> 40) & 0xffu;
             const uint64_t base = ((const uint64_t*)op.aux)[win];
             if (base) dst = base + (v & kPostOffMask);
-            else report_error(a, AERR_BAD_WINDOW);
+            else report_error(h, AERR_BAD_WINDOW);
         } else {
-            report_error(a, AERR_TIMEOUT_POST);
+            report_error(h, AERR_TIMEOUT_POST);
         }
         *smem_slot = dst;
     }
@@ -269,17 +290,45 @@ __device__ __forceinline__ uint8_t* send_wait_post(const GroupArgs& a, const OpD
     return (uint8_t*)(*smem_slot);
 }
 
-// After this CTA's stores: the last CTA of the op to get here publishes completion.
-__device__ __forceinline__ void send_signal_done(const OpDesc& op) {
+// After this CTA's accesses: the last CTA of the op to get here publishes completion.
+__device__ __forceinline__ void movers_signal(const OpDesc& op, uint64_t flag) {
     __syncthreads();
     if (threadIdx.x == 0) {
-        fence_sys();  // this CTA's peer stores are performed before the counter moves
+        fence_sys();  // this CTA's peer accesses are performed before the counter moves
         const uint32_t old = atomicInc((uint32_t*)op.arrive, op.nblocks - 1);
-        if (old == op.nblocks - 1) {
-            fence_sys();
-            st_release_sys((uint64_t*)op.signal_flag, op.seq);
-        }
+        if (old == op.nblocks - 1) st_release_sys((uint64_t*)flag, op.seq);  // release = fence + store
     }
+}
+
+// Receive of a large message.  The sender's word says either where its payload lies (the
+// caller then pulls it: returns the peer-mapped source) or that it will push (then CTA 0 posts
+// this rank's buffer and waits like a control thread; returns nullptr).
+__device__ __forceinline__ const uint8_t* recv_adaptive(const GroupHdr& h, const OpDesc& op, uint32_t part, uint64_t* smem_slot) {
+    if (threadIdx.x == 0) {
+        uint64_t v = 0;
+        if (!wait_word(h, (const uint64_t*)op.f_wait2, op.seq, v)) {
+            report_error(h, AERR_TIMEOUT_POST);
+            v = 0;
+        }
+        *smem_slot = v;
+    }
+    __syncthreads();
+    const uint64_t v = *smem_slot;
+    if (v == 0) return nullptr;
+    const uint32_t win = (uint32_t)(v >> 40) & 0xffu;
+    if (win == kWinPushPlease) {
+        if (part == 0 && threadIdx.x == 0) {
+            if (op.word) post_and_wait(h, op);
+            else report_error(h, AERR_BAD_WINDOW);  // neither side's buffer is registered
+        }
+        return nullptr;
+    }
+    const uint64_t base = ((const uint64_t*)op.aux)[win];
+    if (!base) {
+        if (threadIdx.x == 0) report_error(h, AERR_BAD_WINDOW);
+        return nullptr;
+    }
+    return (const uint8_t*)(base + (v & kPostOffMask));
 }
 
 // ---------------------------------------------------------------- eager (LL) roles
@@ -297,15 +346,15 @@ __device__ __forceinline__ void store_8_bytes_partial(uint8_t* p, uint64_t v, si
     for (int i = 0; i < n; ++i) p[i] = (uint8_t)(v >> (8 * i));
 }
 
-__device__ __forceinline__ void ll_send(const GroupArgs& a, const OpDesc& op, uint64_t* smem_slot) {
+// CTA `part` of `op.nblocks` handles lines part*blockDim + tid, + nblocks*blockDim, ...
+__device__ __forceinline__ void ll_send(const GroupHdr& h, const OpDesc& op, uint32_t part, uint64_t* smem_slot) {
     // slot reuse: the receiver acknowledged message seq - kLLSlots in this slot
     if (threadIdx.x == 0) {
         uint64_t ok = 1, v;
         if (op.seq > (uint64_t)kLLSlots) {
             const uint64_t want = op.seq - kLLSlots;
-            if (!spin_flag((const uint64_t*)op.wait_flag, a.timeout_ns, v,
-                           [want](uint64_t x) { return x == want; })) {
-                report_error(a, AERR_TIMEOUT_LL_ACK);
+            if (!spin_flag((const uint64_t*)op.f_wait, h.timeout_ns, v, [want](uint64_t x) { return x == want; })) {
+                report_error(h, AERR_TIMEOUT_LL_ACK);
                 ok = 0;
             }
         }
@@ -317,20 +366,29 @@ __device__ __forceinline__ void ll_send(const GroupArgs& a, const OpDesc& op, ui
     uint8_t* ring = (uint8_t*)op.aux;
     const size_t nlines = op.nbytes ? (op.nbytes + 7) / 8 : 1;  // a 0-byte message still needs a flag
     const uint32_t flag = (uint32_t)op.seq;
-    for (size_t e = threadIdx.x; e < nlines; e += blockDim.x) {
+    const size_t stride = (size_t)op.nblocks * blockDim.x;
+    const bool fast = ((uint64_t)src & 7) == 0;
+    size_t e = (size_t)part * blockDim.x + threadIdx.x;
+    const size_t full = op.nbytes / 8;  // lines that carry 8 whole payload bytes
+    if (fast) {
+#pragma unroll 4
+        for (; e < full; e += stride) st_ll_line(ring + e * 16, *(const uint64_t*)(src + e * 8), flag);
+    }
+    for (; e < nlines; e += stride) {
         const size_t off = e * 8;
         const uint64_t data = off < op.nbytes ? load_8_bytes_partial(src + off, op.nbytes - off) : 0;
         st_ll_line(ring + e * 16, data, flag);
     }
 }
 
-__device__ __forceinline__ void ll_recv(const GroupArgs& a, const OpDesc& op) {
+__device__ __forceinline__ void ll_recv(const GroupHdr& h, const OpDesc& op, uint32_t part) {
     uint8_t* dst = (uint8_t*)op.local;
     const uint8_t* ring = (const uint8_t*)op.aux;
     const size_t nlines = op.nbytes ? (op.nbytes + 7) / 8 : 1;
     const uint32_t flag = (uint32_t)op.seq;
+    const size_t stride = (size_t)op.nblocks * blockDim.x;
     bool failed = false;
-    for (size_t e = threadIdx.x; e < nlines && !failed; e += blockDim.x) {
+    for (size_t e = (size_t)part * blockDim.x + threadIdx.x; e < nlines && !failed; e += stride) {
         uint4 line = ld_ll_line(ring + e * 16);
         if (line.y != flag || line.w != flag) {
             const uint64_t t0 = globaltimer_ns();
@@ -338,35 +396,90 @@ __device__ __forceinline__ void ll_recv(const GroupArgs& a, const OpDesc& op) {
             for (;;) {
                 line = ld_ll_line(ring + e * 16);
                 if (line.y == flag && line.w == flag) break;
-                if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > a.timeout_ns) { failed = true; break; }
+                if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > h.timeout_ns) { failed = true; break; }
             }
         }
-        if (failed) { report_error(a, AERR_TIMEOUT_LL_DATA); break; }
+        if (failed) { report_error(h, AERR_TIMEOUT_LL_DATA); break; }
         const size_t off = e * 8;
         if (off < op.nbytes)
             store_8_bytes_partial(dst + off, (uint64_t)line.x | ((uint64_t)line.z << 32), op.nbytes - off);
     }
     __syncthreads();
-    // slot may be overwritten once the sender sees this
-    if (threadIdx.x == 0) st_release_sys((uint64_t*)op.signal_flag, op.seq);
+    // The slot may be overwritten once the sender sees the ack; the last CTA to finish sends it.
+    // Every line of the slot has been loaded and consumed by then (the barrier above), so the
+    // ack needs no fence of its own: a relaxed system-scope store keeps MEMBAR.SYS off the
+    // latency path.
+    if (threadIdx.x == 0) {
+        if (op.nblocks == 1) {
+            st_relaxed_sys((uint64_t*)op.f_signal, op.seq);
+        } else {
+            __threadfence();
+            const uint32_t old = atomicInc((uint32_t*)op.arrive, op.nblocks - 1);
+            if (old == op.nblocks - 1) st_relaxed_sys((uint64_t*)op.f_signal, op.seq);
+        }
+    }
 }
 
 // ---------------------------------------------------------------- dispatch
 
-__device__ __forceinline__ const OpDesc* find_op(const GroupArgs& a, uint32_t bid) {
-    for (uint32_t i = 0; i < a.nops; ++i) {
-        const OpDesc& op = a.ops[i];
-        if (op.kind != OP_RECV_RDV && bid >= op.first_block && bid < op.first_block + op.nblocks) return &op;
+__device__ __forceinline__ const OpDesc* find_op(const GroupHdr& h, const OpDesc* ops, uint32_t bid) {
+    for (uint32_t i = 0; i < h.nops; ++i) {
+        const OpDesc& op = ops[i];
+        if (op.kind != OP_POST && bid >= op.first_block && bid < op.first_block + op.nblocks) return &op;
     }
     return nullptr;
 }
 
-// Control CTA: thread t serves the t-th rendezvous receive of the group.
-__device__ __forceinline__ void run_ctrl(const GroupArgs& a) {
+// Control CTA: thread t serves the t-th OP_POST of the group.
+__device__ __forceinline__ void run_ctrl(const GroupHdr& h, const OpDesc* ops) {
     uint32_t seen = 0;
-    for (uint32_t i = 0; i < a.nops; ++i) {
-        if (a.ops[i].kind != OP_RECV_RDV) continue;
-        if (seen++ == threadIdx.x) { ctrl_recv(a, a.ops[i]); return; }
+    for (uint32_t i = 0; i < h.nops; ++i) {
+        if (ops[i].kind != OP_POST) continue;
+        if (seen++ == threadIdx.x) { post_and_wait(h, ops[i]); return; }
+    }
+}
+
+// What a mover CTA has to copy once its role has been resolved.
+struct CopyJob {
+    uint8_t* dst;
+    const uint8_t* src;
+    uint64_t signal;     // flag the last CTA publishes afterwards (0: none)
+    const OpDesc* op;
+    uint32_t part;
+    bool is_push;        // destination is peer memory (the TMA flavour stages these)
+};
+
+// Runs the control / eager roles to completion and resolves the mover roles to a CopyJob, so
+// that each kernel has exactly one inlined copy loop.  Returns false when this CTA is done.
+__device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* ops, uint64_t* slot, CopyJob& job) {
+    const uint32_t bid = blockIdx.x;
+    if (h.n_ctrl && bid == 0) { run_ctrl(h, ops); return false; }
+    const OpDesc* op = find_op(h, ops, bid);
+    if (!op) return false;
+    const uint32_t part = bid - op->first_block;
+    job.op = op;
+    job.part = part;
+    job.is_push = false;
+    switch (op->kind) {
+        case OP_PUSH:
+            job.dst = push_wait_post(h, *op, part, slot);
+            job.src = (const uint8_t*)op->local;
+            job.signal = op->f_signal;
+            job.is_push = true;
+            return job.dst != nullptr;
+        case OP_COPY:
+            job.dst = (uint8_t*)op->aux;
+            job.src = (const uint8_t*)op->local;
+            job.signal = 0;
+            return true;
+        case OP_RECV_ADAPT:
+            job.src = recv_adaptive(h, *op, part, slot);
+            job.dst = (uint8_t*)op->local;
+            job.signal = op->f_signal2;
+            return job.src != nullptr;
+        case OP_SEND_LL: ll_send(h, *op, part, slot); return false;
+        case OP_RECV_LL: ll_recv(h, *op, part); return false;
+        default: return false;
     }
 }
 

@@ -29,6 +29,7 @@ struct BootBlob {
     uint64_t host_hash;
     int32_t pid, device;
     uint64_t eager_bytes;
+    int64_t pull_min_bytes;
     uint64_t ctl_bytes;
     char pci_bus_id[32];
     cudaIpcMemHandle_t ctl_handle;
@@ -48,9 +49,13 @@ static_assert(sizeof(RegBlob) <= kRegBlobBytes, "register blob too large");
 //   post[]   the peer, as receiver of my sends   (I poll it as sender)
 //   done[]   the peer, as sender to me           (I poll it as receiver)
 //   ll_ack[] the peer, as eager receiver         (I poll it as eager sender)
+//   pull_post[] the peer, as sender of a large message to me: where its payload lies / "I will push"
+//   pull_done[] the peer, as receiver that pulled from me   (I poll it as sender)
 struct PeerCtl {
     uint64_t post[kRing];
     uint64_t done[kRing];
+    uint64_t pull_post[kRing];
+    uint64_t pull_done[kRing];
     uint64_t ll_ack[kLLSlots];
     uint64_t pad[8];
 };
@@ -77,15 +82,22 @@ struct PendingOp {
 };
 
 struct Options {
-    long long path = 0;        // 0 auto, 1 ldst, 2 tma, 3 ce
-    long long nblocks = 0;     // CTAs per send to a peer, 0 auto
-    long long self_nblocks = 0;
-    long long eager_bytes = 16 * 1024;
+    long long path = 0;            // 0 auto, 1 ldst, 2 tma, 3 ce
+    long long nblocks = 0;         // CTAs per push to a peer, 0 auto
+    long long self_nblocks = 0;    // CTAs of a local copy, 0 auto
+    long long pull_nblocks = 0;    // CTAs that pull a large message, 0 auto
+    long long eager_nblocks = 0;   // most CTAs an eager message may use, 0 auto
+    long long eager_bytes = 1 << 20;   // measured on 2xB200: the eager ring beats the rendezvous push up to 1 MiB
+    long long pull_min_bytes = 4 << 20;  // messages at least this large let the receiver pull (-1: never); same on all ranks
     long long timeout_ms = 20000;
-    long long vec_bytes = 16;
-    long long tma_chunk = 16 * 1024;
-    long long tma_stages = 8;
-    long long tma_min_bytes = -1;  // auto: sizes at or above this use the TMA flavour (-1 never)
+    long long tma_chunk = 32 * 1024;
+    long long tma_stages = 6;
+    long long tma_min_bytes = -1;  // auto: pushes at or above this use the TMA flavour (-1 never)
+    long long self_tma_min_bytes = 32 << 20;  // auto: local copies at or above this use the TMA flavour (-1 never)
+    long long pdl = 1;             // programmatic dependent launch: 0 never, 1 eager-only and local-copy groups (where it
+                                   // measured faster), 2 every group (push/pull kernels measured slower with it)
+    long long loopback = 0;        // 1: a send to oneself goes through the wire protocol instead of a plain copy (tests)
+    long long bidir_push = 1;      // a large send whose group also receives a large message from that peer pushes
 };
 
 struct Engine {
@@ -98,7 +110,7 @@ struct Engine {
     size_t ctl_bytes = 0, ll_slot_bytes = 0, ll_off = 0;
     uint8_t* ctl = nullptr;                     // my control region (exported)
     uint8_t* peer_ctl[P2P_MAX_RANKS] = {};      // everyone's, peer-mapped (mine == ctl)
-    uint32_t* arrive = nullptr;                 // [nranks][kRing] local arrival counters
+    uint32_t* arrive = nullptr;                 // local arrival counters: push [nranks][kRing], pull [nranks][kRing], eager [nranks][kLLSlots]
     uint64_t* win_table = nullptr;              // [nranks][P2P_MAX_WINDOWS] device table of mapped bases
     CheckPartial* chk_partials = nullptr;       // scratch for pattern_check
     unsigned int* chk_ticket = nullptr;
@@ -194,40 +206,54 @@ int check_ready() {
 
 // ---- plan selection -----------------------------------------------------------------
 
-struct Plan {
-    int path;      // 1 ldst, 2 tma, 4 eager
-    int nblocks;
-};
+enum Proto { PROTO_EAGER = 4, PROTO_PUSH = 1, PROTO_LARGE = 5, PROTO_COPY = 6 };
 
-Plan plan_for(size_t nbytes, int peer) {
-    Plan p{};
-    if ((long long)nbytes <= g.opt.eager_bytes) {
-        p.path = 4;
-        p.nblocks = 1;
-        return p;
-    }
-    const bool self = (peer == g.rank);
-    int path = (int)g.opt.path;
-    if (path == 0 || path == 3)
-        path = (g.opt.tma_min_bytes >= 0 && (long long)nbytes >= g.opt.tma_min_bytes) ? 2 : 1;
-    p.path = path;
-    if (path == 2) {
-        const size_t chunks = (nbytes + (size_t)g.opt.tma_chunk - 1) / (size_t)g.opt.tma_chunk;
-        long long cap = self ? (g.opt.self_nblocks ? g.opt.self_nblocks : g.sm_count * g.ctas_tma)
-                             : (g.opt.nblocks ? g.opt.nblocks : 32);
-        // keep every CTA's ring busy: at least two chunks each
-        p.nblocks = (int)std::max<size_t>(1, std::min<size_t>((chunks + 1) / 2, (size_t)cap));
-    } else {
-        const size_t tile = (size_t)kLdstThreads * 128;  // bytes one CTA moves per loop trip
-        const size_t tiles = (nbytes + tile - 1) / tile;
-        long long cap = self ? (g.opt.self_nblocks ? g.opt.self_nblocks : g.sm_count * g.ctas_ldst)
-                             : (g.opt.nblocks ? g.opt.nblocks : 32);
-        p.nblocks = (int)std::max<size_t>(1, std::min<size_t>(tiles, (size_t)cap));
-    }
-    return p;
+inline bool is_large(size_t nbytes) { return g.opt.pull_min_bytes >= 0 && (long long)nbytes >= g.opt.pull_min_bytes; }
+
+inline Proto proto_for(size_t nbytes) {
+    if ((long long)nbytes <= g.opt.eager_bytes) return PROTO_EAGER;
+    return is_large(nbytes) ? PROTO_LARGE : PROTO_PUSH;
 }
 
-int find_window(const void* buf, size_t nbytes, uint32_t* win, uint64_t* off) {
+inline int eager_ctas(size_t nbytes) {
+    // 4096 lines (32 KiB of payload) per CTA
+    const size_t n = (nbytes + 32767) / 32768;
+    const long long cap = g.opt.eager_nblocks ? g.opt.eager_nblocks : 32;  // 1 MiB: 32 CTAs 8.6 us vs 16 CTAs 9.9 us per message
+    return (int)std::max<size_t>(1, std::min<size_t>(n, (size_t)cap));
+}
+
+// flavour of the kernel a push of this size would like (1 ldst, 2 tma)
+inline int push_flavour(size_t nbytes) {
+    int path = (int)g.opt.path;
+    if (path == 0 || path == 3) path = (g.opt.tma_min_bytes >= 0 && (long long)nbytes >= g.opt.tma_min_bytes) ? 2 : 1;
+    return path;
+}
+
+// flavour a matched send-to-self (local copy) would like: measured on B200, the TMA ring with one CTA
+// per SM is the fastest large HBM copy (96% of the measured copy peak at 256 MiB), ld/st the fastest small one
+inline int self_copy_flavour(size_t nbytes) {
+    if (g.opt.path == 1 || g.opt.path == 2) return (int)g.opt.path;
+    return (g.opt.self_tma_min_bytes >= 0 && (long long)nbytes >= g.opt.self_tma_min_bytes) ? 2 : 1;
+}
+
+// CTAs that move `nbytes`: `flavour` of the launch, destination class decides the cap
+inline int mover_ctas(size_t nbytes, int flavour, bool self, bool pull) {
+    if (flavour == FLAVOUR_TMA && !pull) {
+        const size_t chunks = (nbytes + (size_t)g.opt.tma_chunk - 1) / (size_t)g.opt.tma_chunk;
+        const long long cap = self ? (g.opt.self_nblocks ? g.opt.self_nblocks : (long long)g.sm_count * g.ctas_tma)
+                                   : (g.opt.nblocks ? g.opt.nblocks : 32);
+        return (int)std::max<size_t>(1, std::min<size_t>((chunks + 1) / 2, (size_t)cap));  // >= 2 chunks per ring
+    }
+    const size_t tile = (size_t)kLdstThreads * 128;  // bytes one CTA moves per loop trip
+    const size_t tiles = (nbytes + tile - 1) / tile;
+    long long cap;
+    if (self) cap = g.opt.self_nblocks ? g.opt.self_nblocks : (long long)g.sm_count;  // 1 CTA per SM beat 2 (6.17 vs 6.02 TB/s)
+    else if (pull) cap = g.opt.pull_nblocks ? g.opt.pull_nblocks : 64;
+    else cap = g.opt.nblocks ? g.opt.nblocks : 32;
+    return (int)std::max<size_t>(1, std::min<size_t>(tiles, (size_t)cap));
+}
+
+bool lookup_window(const void* buf, size_t nbytes, uint32_t* win, uint64_t* off) {
     const uint8_t* b = (const uint8_t*)buf;
     for (int w = 0; w < P2P_MAX_WINDOWS; ++w) {
         const Window& W = g.windows[w];
@@ -235,15 +261,15 @@ int find_window(const void* buf, size_t nbytes, uint32_t* win, uint64_t* off) {
         if (b >= W.base && b + nbytes <= W.base + W.bytes) {
             *win = (uint32_t)w;
             *off = (uint64_t)(b - W.base);
-            return P2P_SUCCESS;
+            return true;
         }
     }
-    return fail(P2P_INVALID_USAGE,
-                "p2p_recv: buffer %p (+%zu bytes) is not inside a registered window; messages larger than "
-                "the eager limit (%lld bytes) are stored directly into the receive buffer by the sender and "
-                "need p2p_register_export/import first",
-                buf, nbytes, g.opt.eager_bytes);
+    return false;
 }
+
+inline uint32_t* arrive_push(int p, uint64_t seq) { return g.arrive + (size_t)p * kRing + seq % kRing; }
+inline uint32_t* arrive_pull(int p, uint64_t seq) { return g.arrive + (size_t)(g.nranks + p) * kRing + seq % kRing; }
+inline uint32_t* arrive_ll(int p, uint64_t seq) { return g.arrive + (size_t)2 * g.nranks * kRing + (size_t)p * kLLSlots + seq % kLLSlots; }
 
 // ---- group launch --------------------------------------------------------------------
 
@@ -251,117 +277,209 @@ int launch_pending() {
     std::vector<PendingOp> ops;
     ops.swap(g.group_ops);
     if (ops.empty()) return P2P_SUCCESS;
-    if (ops.size() > (size_t)kMaxGroupOps)
-        return fail(P2P_INVALID_USAGE, "a group holds at most %d operations (got %zu)", kMaxGroupOps, ops.size());
+    const int me = g.rank;
+
+    // a send to oneself and a receive from oneself in the same group are one local copy
+    std::vector<int> partner(ops.size(), -1);
+    if (!g.opt.loopback) {
+        std::vector<size_t> self_sends, self_recvs;
+        for (size_t i = 0; i < ops.size(); ++i)
+            if (ops[i].peer == me) (ops[i].is_send ? self_sends : self_recvs).push_back(i);
+        for (size_t k = 0; k < std::min(self_sends.size(), self_recvs.size()); ++k) {
+            const size_t si = self_sends[k], ri = self_recvs[k];
+            if (ops[si].nbytes != ops[ri].nbytes)
+                return fail(P2P_INVALID_ARGUMENT, "send to self of %zu bytes is matched by a receive of %zu bytes", ops[si].nbytes,
+                            ops[ri].nbytes);
+            partner[si] = (int)ri;
+            partner[ri] = (int)si;
+        }
+    }
 
     // validate everything before any sequence number moves
-    struct Resolved { Plan plan; uint32_t win; uint64_t off; };
+    struct Resolved { Proto proto; uint32_t win; uint64_t off; bool registered; bool pull_send; int nblocks; };
     std::vector<Resolved> res(ops.size());
     int flavour = FLAVOUR_LDST;
+    size_t nops_out = 0;
     for (size_t i = 0; i < ops.size(); ++i) {
         const PendingOp& op = ops[i];
-        res[i].plan = plan_for(op.nbytes, op.peer);
-        res[i].win = 0;
-        res[i].off = 0;
-        if (res[i].plan.path != 4 && !op.is_send) {
-            int rc = find_window(op.buf, op.nbytes, &res[i].win, &res[i].off);
-            if (rc) return rc;
+        Resolved& r = res[i];
+        r = Resolved{};
+        if (partner[i] >= 0) {
+            r.proto = PROTO_COPY;
+            if (op.is_send) {
+                ++nops_out;
+                if (self_copy_flavour(op.nbytes) == 2) flavour = FLAVOUR_TMA;
+            }
+            continue;
         }
-        if (res[i].plan.path == 2 && op.is_send) flavour = FLAVOUR_TMA;
+        r.proto = proto_for(op.nbytes);
+        ++nops_out;
+        if (r.proto == PROTO_EAGER) continue;
+        r.registered = lookup_window(op.buf, op.nbytes, &r.win, &r.off);
+        if (!op.is_send && r.proto == PROTO_PUSH && !r.registered)
+            return fail(P2P_INVALID_USAGE,
+                        "p2p_recv: buffer %p (+%zu bytes) is not inside a registered window; messages between the eager limit "
+                        "(%lld bytes) and the pull threshold (%lld bytes) are stored directly into the receive buffer by the "
+                        "sender and need p2p_register_export/import first",
+                        op.buf, op.nbytes, g.opt.eager_bytes, g.opt.pull_min_bytes);
+        if (op.is_send && r.proto == PROTO_LARGE) {
+            // the sender decides: let the receiver pull when it can map my buffer, unless this group also
+            // receives a large message from the same peer (both directions busy: pushes interfere less)
+            bool also_receiving = false;
+            for (size_t j = 0; j < ops.size(); ++j)
+                if (!ops[j].is_send && ops[j].peer == op.peer && partner[j] < 0 && is_large(ops[j].nbytes)) also_receiving = true;
+            if (!g.opt.bidir_push) also_receiving = false;
+            r.pull_send = r.registered && !also_receiving && g.opt.path != 2 && g.opt.path != 1;
+        }
+        if (op.is_send && !(r.proto == PROTO_LARGE && r.pull_send) && push_flavour(op.nbytes) == 2) flavour = FLAVOUR_TMA;
     }
-    if (flavour == FLAVOUR_TMA) {
-        // one flavour per launch: re-plan ld/st sends of this group for the TMA kernel
-        const long long keep = g.opt.path;
-        g.opt.path = 2;
+    if (nops_out > (size_t)kMaxGroupOps)
+        return fail(P2P_INVALID_USAGE, "a group holds at most %d operations (got %zu)", kMaxGroupOps, nops_out);
+
+    // CTA counts
+    const int per_sm = flavour == FLAVOUR_TMA ? g.ctas_tma : g.ctas_ldst;
+    long long budget = (long long)g.sm_count * per_sm;
+    long long fixed = 0, want = 0;
+    uint32_t n_ctrl = 0;
+    size_t eager_total = 0;
+    bool only_small = true;
+    for (size_t i = 0; i < ops.size(); ++i) {
+        const PendingOp& op = ops[i];
+        Resolved& r = res[i];
+        const bool self = op.peer == me;
+        switch (r.proto) {
+            case PROTO_COPY:
+                r.nblocks = op.is_send ? mover_ctas(op.nbytes, flavour, true, false) : 0;
+                want += r.nblocks;
+                if (op.nbytes > 4096) only_small = false;
+                break;
+            case PROTO_EAGER:
+                r.nblocks = eager_ctas(op.nbytes);
+                fixed += r.nblocks;
+                eager_total += op.nbytes;
+                break;
+            case PROTO_PUSH:
+                only_small = false;
+                if (op.is_send) { r.nblocks = mover_ctas(op.nbytes, flavour, self, false); want += r.nblocks; }
+                else ++n_ctrl;
+                break;
+            case PROTO_LARGE:
+                only_small = false;
+                if (op.is_send) {
+                    if (r.pull_send) ++n_ctrl;
+                    else { r.nblocks = mover_ctas(op.nbytes, flavour, self, false); want += r.nblocks; }
+                } else {
+                    r.nblocks = mover_ctas(op.nbytes, FLAVOUR_LDST, self, true);
+                    want += r.nblocks;
+                }
+                break;
+        }
+    }
+    budget -= fixed + (n_ctrl ? 1 : 0);
+    if (budget < 1) budget = 1;
+    if (want > budget)
         for (size_t i = 0; i < ops.size(); ++i)
-            if (ops[i].is_send && res[i].plan.path == 1) res[i].plan = plan_for(ops[i].nbytes, ops[i].peer);
-        g.opt.path = keep;
-    }
+            if (res[i].nblocks > 0 && res[i].proto != PROTO_EAGER)
+                res[i].nblocks = (int)std::max<long long>(1, res[i].nblocks * budget / want);
 
     GroupArgs args;
     memset(&args, 0, sizeof args);
-    args.vec_bytes = (uint32_t)g.opt.vec_bytes;
-    args.tma_chunk = (uint32_t)g.opt.tma_chunk;
-    args.tma_stages = (uint32_t)g.opt.tma_stages;
-    args.timeout_ns = (uint64_t)g.opt.timeout_ms * 1000000ull;
-    args.async_err = g.async_err_dev;
-
-    // CTA budget: everything should be co-resident so that no role waits for an SM
-    const int per_sm = flavour == FLAVOUR_TMA ? g.ctas_tma : g.ctas_ldst;
-    long long budget = (long long)g.sm_count * per_sm;
-    uint32_t n_ctrl = 0, n_fixed = 0;
-    long long want_send = 0;
-    for (size_t i = 0; i < ops.size(); ++i) {
-        if (res[i].plan.path == 4) ++n_fixed;
-        else if (!ops[i].is_send) ++n_ctrl;
-        else want_send += res[i].plan.nblocks;
-    }
-    budget -= n_fixed + (n_ctrl ? 1 : 0);
-    if (budget < 1) budget = 1;
-    if (want_send > budget) {
-        for (size_t i = 0; i < ops.size(); ++i)
-            if (ops[i].is_send && res[i].plan.path != 4)
-                res[i].plan.nblocks = (int)std::max<long long>(1, res[i].plan.nblocks * budget / want_send);
-    }
+    args.h.tma_chunk = (uint32_t)g.opt.tma_chunk;
+    args.h.tma_stages = (uint32_t)g.opt.tma_stages;
+    args.h.timeout_ns = (uint64_t)g.opt.timeout_ms * 1000000ull;
+    args.h.async_err = g.async_err_dev;
+    args.h.pdl = 0;  // decided below, once the roles of the group are known
+    args.h.n_ctrl = n_ctrl;
 
     uint32_t next_block = n_ctrl ? 1 : 0;
-    args.n_ctrl = n_ctrl;
     uint8_t* my = g.ctl;
-    const int me = g.rank;
-    // order: eager receives, eager sends, then the rendezvous pushes (control CTA is block 0)
-    for (int pass = 0; pass < 4; ++pass) {
+    // order of CTAs: control CTA, eager receives, eager sends, large receives (they start by waiting),
+    // then everything that pushes or copies
+    for (int pass = 0; pass < 5; ++pass) {
         for (size_t i = 0; i < ops.size(); ++i) {
             const PendingOp& op = ops[i];
-            const bool eager = res[i].plan.path == 4;
-            const int cls = !op.is_send ? (eager ? 1 : 0) : (eager ? 2 : 3);
+            const Resolved& r = res[i];
+            int cls;
+            if (r.proto == PROTO_COPY) cls = op.is_send ? 4 : -1;
+            else if (r.proto == PROTO_EAGER) cls = op.is_send ? 2 : 1;
+            else if (r.proto == PROTO_PUSH) cls = op.is_send ? 4 : 0;
+            else cls = op.is_send ? (r.pull_send ? 0 : 4) : 3;
             if (cls != pass) continue;
-            OpDesc& d = args.ops[args.nops++];
+            OpDesc& d = args.ops[args.h.nops++];
             const int p = op.peer;
             uint8_t* theirs = g.peer_ctl[p];
             d.local = (uint64_t)op.buf;
             d.nbytes = op.nbytes;
             d.peer = (uint32_t)p;
-            if (cls == 0) {  // rendezvous receive
-                const uint64_t seq = ++g.rdv_recv_seq[p];
-                d.kind = OP_RECV_RDV;
-                d.seq = seq;
-                d.word = make_post_word(seq, res[i].win, res[i].off);
-                d.signal_flag = (uint64_t)&peer_section(theirs, me)->post[seq % kRing];
-                d.wait_flag = (uint64_t)&peer_section(my, p)->done[seq % kRing];
-            } else if (cls == 1) {  // eager receive
+            d.nblocks = (uint32_t)r.nblocks;
+            if (r.proto == PROTO_COPY) {
+                d.kind = OP_COPY;
+                d.aux = (uint64_t)ops[(size_t)partner[i]].buf;
+            } else if (r.proto == PROTO_EAGER && !op.is_send) {
                 const uint64_t seq = ++g.ll_recv_seq[p];
                 d.kind = OP_RECV_LL;
                 d.seq = seq;
                 d.aux = (uint64_t)ll_slot(my, p, seq);
-                d.signal_flag = (uint64_t)&peer_section(theirs, me)->ll_ack[seq % kLLSlots];
-                d.first_block = next_block;
-                d.nblocks = 1;
-                next_block += 1;
-            } else if (cls == 2) {  // eager send
+                d.f_signal = (uint64_t)&peer_section(theirs, me)->ll_ack[seq % kLLSlots];
+                d.arrive = (uint64_t)arrive_ll(p, seq);
+            } else if (r.proto == PROTO_EAGER) {
                 const uint64_t seq = ++g.ll_send_seq[p];
                 d.kind = OP_SEND_LL;
                 d.seq = seq;
                 d.aux = (uint64_t)ll_slot(theirs, me, seq);
-                d.wait_flag = (uint64_t)&peer_section(my, p)->ll_ack[seq % kLLSlots];
-                d.first_block = next_block;
-                d.nblocks = 1;
-                next_block += 1;
-            } else {  // rendezvous send
-                const uint64_t seq = ++g.rdv_send_seq[p];
-                d.kind = OP_SEND_RDV;
+                d.f_wait = (uint64_t)&peer_section(my, p)->ll_ack[seq % kLLSlots];
+            } else if (!op.is_send) {
+                const uint64_t seq = ++g.rdv_recv_seq[p];
                 d.seq = seq;
-                d.wait_flag = (uint64_t)&peer_section(my, p)->post[seq % kRing];
-                d.signal_flag = (uint64_t)&peer_section(theirs, me)->done[seq % kRing];
-                d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
-                d.arrive = (uint64_t)(g.arrive + (size_t)p * kRing + seq % kRing);
+                // what a pushing sender needs from me
+                d.word = r.registered ? make_post_word(seq, r.win, r.off) : 0;
+                d.f_signal = (uint64_t)&peer_section(theirs, me)->post[seq % kRing];
+                d.f_wait = (uint64_t)&peer_section(my, p)->done[seq % kRing];
+                if (r.proto == PROTO_PUSH) {
+                    d.kind = OP_POST;
+                } else {
+                    d.kind = OP_RECV_ADAPT;
+                    d.f_wait2 = (uint64_t)&peer_section(my, p)->pull_post[seq % kRing];
+                    d.f_signal2 = (uint64_t)&peer_section(theirs, me)->pull_done[seq % kRing];
+                    d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
+                    d.arrive = (uint64_t)arrive_pull(p, seq);
+                }
+            } else {
+                const uint64_t seq = ++g.rdv_send_seq[p];
+                d.seq = seq;
+                if (r.proto == PROTO_LARGE && r.pull_send) {
+                    d.kind = OP_POST;  // publish where my payload lies, wait until it has been read
+                    d.word = make_post_word(seq, r.win, r.off);
+                    d.f_signal = (uint64_t)&peer_section(theirs, me)->pull_post[seq % kRing];
+                    d.f_wait = (uint64_t)&peer_section(my, p)->pull_done[seq % kRing];
+                } else {
+                    d.kind = OP_PUSH;
+                    d.f_wait = (uint64_t)&peer_section(my, p)->post[seq % kRing];
+                    d.f_signal = (uint64_t)&peer_section(theirs, me)->done[seq % kRing];
+                    d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
+                    d.arrive = (uint64_t)arrive_push(p, seq);
+                    if (r.proto == PROTO_LARGE) {  // the receiver is waiting to be told
+                        d.f_signal2 = (uint64_t)&peer_section(theirs, me)->pull_post[seq % kRing];
+                        d.word2 = make_post_word(seq, kWinPushPlease, 0);
+                    }
+                }
+            }
+            if (d.kind != OP_POST) {
                 d.first_block = next_block;
-                d.nblocks = (uint32_t)res[i].plan.nblocks;
                 next_block += d.nblocks;
             }
         }
     }
     const uint32_t grid = next_block;
     if (grid == 0) return P2P_SUCCESS;
+    bool light = true;  // no rendezvous role in the group
+    for (uint32_t i = 0; i < args.h.nops; ++i) {
+        const uint32_t k = args.ops[i].kind;
+        if (k == OP_POST || k == OP_PUSH || k == OP_RECV_ADAPT) light = false;
+    }
+    args.h.pdl = (g.opt.pdl == 2 || (g.opt.pdl == 1 && light)) ? 1 : 0;
+    // small eager-only groups run with 128-thread CTAs: less to launch on the latency path
+    const uint32_t block = (flavour == FLAVOUR_LDST && only_small && eager_total <= 8192) ? 128 : kLdstThreads;
 
     // streams: launch on the first op's stream; the others wait for the kernel and it for them
     cudaStream_t launch_stream = ops[0].stream;
@@ -379,7 +497,7 @@ int launch_pending() {
         CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ev_pool[i], 0));
     }
     const int dyn_smem = flavour == FLAVOUR_TMA ? (int)(g.opt.tma_chunk * g.opt.tma_stages) : 0;
-    CUDA_TRY(launch_group(flavour, args, grid, dyn_smem, launch_stream));
+    CUDA_TRY(launch_group(flavour, args, grid, block, dyn_smem, launch_stream));
     if (!others.empty()) {
         CUDA_TRY(cudaEventRecord(g.ev_done, launch_stream));
         for (cudaStream_t s : others) CUDA_TRY(cudaStreamWaitEvent(s, g.ev_done, 0));
@@ -492,10 +610,16 @@ int p2p_init(int rank, int nranks, int device) {
     o.self_nblocks = env_ll("P2P_SELF_NBLOCKS", o.self_nblocks);
     o.eager_bytes = env_ll("P2P_EAGER_BYTES", o.eager_bytes);
     o.timeout_ms = env_ll("P2P_TIMEOUT_MS", o.timeout_ms);
-    o.vec_bytes = env_ll("P2P_VEC_BYTES", o.vec_bytes);
+    o.pull_nblocks = env_ll("P2P_PULL_NBLOCKS", o.pull_nblocks);
+    o.eager_nblocks = env_ll("P2P_EAGER_NBLOCKS", o.eager_nblocks);
+    o.pull_min_bytes = env_ll("P2P_PULL_MIN_BYTES", o.pull_min_bytes);
+    o.pdl = env_ll("P2P_PDL", o.pdl);
+    o.loopback = env_ll("P2P_LOOPBACK", o.loopback);
+    o.bidir_push = env_ll("P2P_BIDIR_PUSH", o.bidir_push);
     o.tma_chunk = env_ll("P2P_TMA_CHUNK", o.tma_chunk);
     o.tma_stages = env_ll("P2P_TMA_STAGES", o.tma_stages);
     o.tma_min_bytes = env_ll("P2P_TMA_MIN_BYTES", o.tma_min_bytes);
+    o.self_tma_min_bytes = env_ll("P2P_SELF_TMA_MIN_BYTES", o.self_tma_min_bytes);
     if (o.eager_bytes < 0 || o.eager_bytes > (1 << 20))
         return fail(P2P_INVALID_ARGUMENT, "P2P_EAGER_BYTES %lld outside [0, 1 MiB]", o.eager_bytes);
 
@@ -506,8 +630,9 @@ int p2p_init(int rank, int nranks, int device) {
     g.ctl_bytes = g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes;
     CUDA_TRY(cudaMalloc(&g.ctl, g.ctl_bytes));
     CUDA_TRY(cudaMemset(g.ctl, 0, g.ctl_bytes));
-    CUDA_TRY(cudaMalloc(&g.arrive, sizeof(uint32_t) * (size_t)nranks * kRing));
-    CUDA_TRY(cudaMemset(g.arrive, 0, sizeof(uint32_t) * (size_t)nranks * kRing));
+    const size_t arrive_words = (size_t)nranks * (2 * kRing + kLLSlots);
+    CUDA_TRY(cudaMalloc(&g.arrive, sizeof(uint32_t) * arrive_words));
+    CUDA_TRY(cudaMemset(g.arrive, 0, sizeof(uint32_t) * arrive_words));
     CUDA_TRY(cudaMalloc(&g.win_table, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
     CUDA_TRY(cudaMemset(g.win_table, 0, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
     CUDA_TRY(cudaMalloc(&g.chk_partials, sizeof(CheckPartial) * (size_t)g.sm_count * 8));
@@ -549,6 +674,7 @@ int p2p_export(void* blob) {
     b.pid = (int32_t)getpid();
     b.device = g.device;
     b.eager_bytes = (uint64_t)g.opt.eager_bytes;
+    b.pull_min_bytes = g.opt.pull_min_bytes;
     b.ctl_bytes = g.ctl_bytes;
     CUDA_TRY(cudaDeviceGetPCIBusId(b.pci_bus_id, sizeof b.pci_bus_id, g.device));
     if (g.nranks > 1) CUDA_TRY(cudaIpcGetMemHandle(&b.ctl_handle, g.ctl));
@@ -574,6 +700,9 @@ int p2p_connect(const void* all_blobs) {
         if (b.eager_bytes != (uint64_t)g.opt.eager_bytes)
             return fail(P2P_INVALID_USAGE, "rank %d uses eager_bytes=%llu, this rank %lld; they must match", r,
                         (unsigned long long)b.eager_bytes, g.opt.eager_bytes);
+        if (b.pull_min_bytes != g.opt.pull_min_bytes)
+            return fail(P2P_INVALID_USAGE, "rank %d uses pull_min_bytes=%lld, this rank %lld; they must match", r,
+                        (long long)b.pull_min_bytes, g.opt.pull_min_bytes);
         if (r == g.rank) continue;
         if (b.ctl_bytes != g.ctl_bytes)
             return fail(P2P_INTERNAL_ERROR, "rank %d control region is %llu bytes, mine %zu", r,
@@ -806,10 +935,16 @@ static long long* option_slot(const char* name) {
     if (!strcmp(name, "self_nblocks")) return &o.self_nblocks;
     if (!strcmp(name, "eager_bytes")) return &o.eager_bytes;
     if (!strcmp(name, "timeout_ms")) return &o.timeout_ms;
-    if (!strcmp(name, "vec_bytes")) return &o.vec_bytes;
+    if (!strcmp(name, "pull_nblocks")) return &o.pull_nblocks;
+    if (!strcmp(name, "eager_nblocks")) return &o.eager_nblocks;
+    if (!strcmp(name, "pull_min_bytes")) return &o.pull_min_bytes;
+    if (!strcmp(name, "pdl")) return &o.pdl;
+    if (!strcmp(name, "loopback")) return &o.loopback;
+    if (!strcmp(name, "bidir_push")) return &o.bidir_push;
     if (!strcmp(name, "tma_chunk")) return &o.tma_chunk;
     if (!strcmp(name, "tma_stages")) return &o.tma_stages;
     if (!strcmp(name, "tma_min_bytes")) return &o.tma_min_bytes;
+    if (!strcmp(name, "self_tma_min_bytes")) return &o.self_tma_min_bytes;
     return nullptr;
 }
 
@@ -826,8 +961,8 @@ int p2p_set_option(const char* name, long long value) {
                         value, g.ll_slot_bytes / 2);
     } else if (!strcmp(name, "path")) {
         if (value < 0 || value > 3) return fail(P2P_INVALID_ARGUMENT, "path must be 0..3");
-    } else if (!strcmp(name, "vec_bytes")) {
-        if (value != 16 && value != 32) return fail(P2P_INVALID_ARGUMENT, "vec_bytes must be 16 or 32");
+    } else if (!strcmp(name, "pull_min_bytes")) {
+        return fail(P2P_INVALID_USAGE, "pull_min_bytes is agreed between ranks at p2p_connect; set P2P_PULL_MIN_BYTES before p2p_init");
     } else if (!strcmp(name, "tma_chunk") || !strcmp(name, "tma_stages")) {
         long long chunk = !strcmp(name, "tma_chunk") ? value : g.opt.tma_chunk;
         long long stages = !strcmp(name, "tma_stages") ? value : g.opt.tma_stages;
@@ -839,7 +974,7 @@ int p2p_set_option(const char* name, long long value) {
         int n = 1;
         if (occupancy(FLAVOUR_TMA, (int)(g.opt.tma_chunk * g.opt.tma_stages), &n) == cudaSuccess && n >= 1) g.ctas_tma = n;
         return P2P_SUCCESS;
-    } else if (value < 0 && strcmp(name, "tma_min_bytes")) {
+    } else if (value < 0 && strcmp(name, "tma_min_bytes") && strcmp(name, "self_tma_min_bytes")) {
         return fail(P2P_INVALID_ARGUMENT, "option '%s' must be >= 0", name);
     }
     *slot = value;
@@ -864,9 +999,17 @@ int p2p_query_plan(size_t bytes, int peer, int* path, int* nblocks) {
     int rc = check_ready();
     if (rc) return rc;
     if (peer < 0 || peer >= g.nranks) return fail(P2P_INVALID_ARGUMENT, "peer %d out of range", peer);
-    Plan p = plan_for(bytes, peer);
-    if (path) *path = p.path;
-    if (nblocks) *nblocks = p.nblocks;
+    const Proto proto = proto_for(bytes);
+    const bool self = peer == g.rank;
+    int pth, nb;
+    if (proto == PROTO_EAGER) { pth = 4; nb = eager_ctas(bytes); }
+    else if (proto == PROTO_LARGE && g.opt.path == 0 && (!self || g.opt.loopback)) { pth = 5; nb = mover_ctas(bytes, FLAVOUR_LDST, self, true); }
+    else {
+        pth = (self && !g.opt.loopback) ? self_copy_flavour(bytes) : push_flavour(bytes);
+        nb = mover_ctas(bytes, pth == 2 ? FLAVOUR_TMA : FLAVOUR_LDST, self, false);
+    }
+    if (path) *path = pth;
+    if (nblocks) *nblocks = nb;
     return P2P_SUCCESS;
 }
 

@@ -47,7 +47,7 @@ int set_last_error(int code, const char* fmt, ...);
 
 cudaError_t configure_kernels(int max_tma_smem);
 cudaError_t occupancy(int flavour, int dyn_smem, int* ctas_per_sm);
-cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, int dyn_smem, cudaStream_t stream);
+cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, uint32_t block, int dyn_smem, cudaStream_t stream);
 uint32_t pattern_grid(size_t nbytes, int sm_count);
 cudaError_t launch_pattern_fill(void* buf, size_t nbytes, uint64_t key, int sm_count, cudaStream_t stream);
 cudaError_t launch_pattern_check(const void* buf, size_t nbytes, uint64_t key, int check, int sm_count,

@@ -7,64 +7,41 @@ namespace p2p {
 
 // ------------------------------------------------------------------ group kernels
 
-// ld/st flavour: 512-thread CTAs, payload moves through registers as 16- or 32-byte
-// coalesced vectors (LDG.E.128/256 + STG.E.128/256 to the peer-mapped address).
+// ld/st flavour: up to 512-thread CTAs, payload moves through registers as 16-byte
+// coalesced vectors (LDG.E.128 + STG.E.128 on the peer-mapped address).
+template <int MAXOPS>
 __global__ void __launch_bounds__(kLdstThreads, 2)
-p2p_group_kernel_ldst(const __grid_constant__ GroupArgs a) {
+p2p_group_kernel_ldst(const __grid_constant__ GroupArgsT<MAXOPS> a) {
     __shared__ uint64_t slot;
-    const uint32_t bid = blockIdx.x;
-    if (a.n_ctrl && bid == 0) { run_ctrl(a); return; }
-    const OpDesc* op = find_op(a, bid);
-    if (!op) return;
-    const uint32_t part = bid - op->first_block;
-    switch (op->kind) {
-        case OP_SEND_RDV: {
-            uint8_t* dst = send_wait_post(a, *op, &slot);
-            if (!dst) return;
-            copy_bytes(dst, (const uint8_t*)op->local, op->nbytes, part, op->nblocks, a.vec_bytes);
-            send_signal_done(*op);
-            break;
-        }
-        case OP_SEND_LL: ll_send(a, *op, &slot); break;
-        case OP_RECV_LL: ll_recv(a, *op); break;
-        default: break;
-    }
+    pdl_prologue(a.h);
+    CopyJob job;
+    if (!resolve_role(a.h, a.ops, &slot, job)) return;
+    copy_bytes(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks);
+    if (job.signal) movers_signal(*job.op, job.signal);
 }
 
-// TMA flavour: 128-thread CTAs, payload staged global -> shared -> peer global by
-// cp.async.bulk (UBLKCP), two elected threads drive the ring.
+// TMA flavour: 128-thread CTAs, a push is staged global -> shared -> peer global by
+// cp.async.bulk (UBLKCP); two elected threads drive the ring.
 __global__ void __launch_bounds__(kTmaThreads, 1)
 p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
     extern __shared__ __align__(128) uint8_t smem_ring[];
     __shared__ uint64_t slot;
     __shared__ __align__(8) uint64_t full[kTmaMaxStages];
     __shared__ __align__(8) uint64_t empty[kTmaMaxStages];
-    const uint32_t bid = blockIdx.x;
-    if (a.n_ctrl && bid == 0) { run_ctrl(a); return; }
-    const OpDesc* op = find_op(a, bid);
-    if (!op) return;
-    const uint32_t part = bid - op->first_block;
-    switch (op->kind) {
-        case OP_SEND_RDV: {
-            if (threadIdx.x == 0) {
-                for (uint32_t i = 0; i < a.tma_stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-                fence_proxy_async();
-            }
-            uint8_t* dst = send_wait_post(a, *op, &slot);  // contains the __syncthreads that publishes the inits
-            if (!dst) return;
-            const uint8_t* src = (const uint8_t*)op->local;
-            if ((((uint64_t)dst ^ (uint64_t)src) & 15) == 0)
-                tma_push(dst, src, op->nbytes, part, op->nblocks, a.tma_chunk, a.tma_stages, smem_ring, full, empty);
-            else
-                copy_bytes(dst, src, op->nbytes, part, op->nblocks, 16);
-            send_signal_done(*op);
-            break;
-        }
-        case OP_SEND_LL: ll_send(a, *op, &slot); break;
-        case OP_RECV_LL: ll_recv(a, *op); break;
-        default: break;
+    if (threadIdx.x == 0) {
+        for (uint32_t i = 0; i < a.h.tma_stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        fence_proxy_async();
     }
+    __syncthreads();
+    pdl_prologue(a.h);
+    CopyJob job;
+    if (!resolve_role(a.h, a.ops, &slot, job)) return;
+    if ((((uint64_t)job.dst ^ (uint64_t)job.src) & 15) == 0)
+        tma_push(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty);
+    else
+        copy_bytes(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks);
+    if (job.signal) movers_signal(*job.op, job.signal);
 }
 
 cudaError_t configure_kernels(int max_tma_smem) {
@@ -74,15 +51,37 @@ cudaError_t configure_kernels(int max_tma_smem) {
 cudaError_t occupancy(int flavour, int dyn_smem, int* ctas_per_sm) {
     if (flavour == FLAVOUR_TMA)
         return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, p2p_group_kernel_tma, kTmaThreads, dyn_smem);
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, p2p_group_kernel_ldst, kLdstThreads, 0);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, p2p_group_kernel_ldst<kMaxGroupOps>, kLdstThreads, 0);
 }
 
-cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, int dyn_smem, cudaStream_t stream) {
-    if (flavour == FLAVOUR_TMA)
-        p2p_group_kernel_tma<<<grid, kTmaThreads, dyn_smem, stream>>>(args);
-    else
-        p2p_group_kernel_ldst<<<grid, kLdstThreads, 0, stream>>>(args);
-    return cudaGetLastError();
+template <typename Args>
+static cudaError_t launch_ex(void (*kernel)(Args), const Args& args, uint32_t grid, uint32_t block, int dyn_smem,
+                             cudaStream_t stream, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = (size_t)dyn_smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args);
+}
+
+cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, uint32_t block, int dyn_smem, cudaStream_t stream) {
+    const bool pdl = args.h.pdl != 0;
+    if (flavour == FLAVOUR_TMA) return launch_ex(p2p_group_kernel_tma, args, grid, kTmaThreads, dyn_smem, stream, pdl);
+    if (args.h.nops <= (uint32_t)kSmallGroupOps) {
+        // same kernel with a 0.5 KB parameter block instead of 3.4 KB: less to copy per launch
+        GroupArgsSmall small;
+        small.h = args.h;
+        for (uint32_t i = 0; i < args.h.nops; ++i) small.ops[i] = args.ops[i];
+        for (uint32_t i = args.h.nops; i < (uint32_t)kSmallGroupOps; ++i) small.ops[i] = OpDesc{};
+        return launch_ex(p2p_group_kernel_ldst<kSmallGroupOps>, small, grid, block, 0, stream, pdl);
+    }
+    return launch_ex(p2p_group_kernel_ldst<kMaxGroupOps>, args, grid, block, 0, stream, pdl);
 }
 
 // ------------------------------------------------------------------ pattern / digest kernels

@@ -14,10 +14,12 @@ struct EngineBackend {
     void init(int, int, int device) { P2PCHECK(p2p_init_mpi(MPI_COMM_WORLD, device)); }
 
     // the reference's cudaMalloc'd buffers stay as they are (p2p_matrix.cc:127-128); the one
-    // added step is making the receive buffer a window peers can store into
-    void buffers(void*, size_t, void* recv, size_t rbytes) {
+    // added step is making them windows: peers store into the receive buffer (push) and, for
+    // large messages, load from the send buffer (pull)
+    void buffers(void* send, size_t sbytes, void* recv, size_t rbytes) {
         int win = -1;
         P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, recv, rbytes, &win));
+        if (!getenv("P2P_NO_SEND_WINDOW")) P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, send, sbytes, &win));
     }
 
     // ncclSend / ncclRecv with ncclInt8 (p2p_matrix.cc:157-161, 165-169)

@@ -35,10 +35,16 @@ def test_reference_loops_verified(built, n, path):
     assert "Evaluating the Bi-Directional NCCL P2P Bandwidth (Gbps)" in out
 
 
-@pytest.mark.parametrize("size", ["8", "1000", "16384", "16385", "1M", "67108864"])
+@pytest.mark.parametrize("size", ["8", "1000", "16385", "1M", "1048577", "3M", "4M", "67108864"])
 def test_pair_sizes_verified(built, size):
     out = matrix(2, "--size", size, "--iters", "3", "--verify", "--timing", "dev", "--warmup", "2")
     assert "verify: OK" in out
+
+
+def test_large_message_with_unregistered_send_buffer(built):
+    """Only the receive buffer is a window: the sender of a large message announces a push."""
+    out = matrix(2, "--size", "8M", "--iters", "3", "--verify", env={"P2P_NO_SEND_WINDOW": "1"})
+    assert "verify: OK" in out and "VERIFY FAILED" not in out
 
 
 def test_allpairs_and_ring_verified(built):

@@ -1,8 +1,10 @@
 """Parity tests on one B200: every data path of the engine, called through the C ABI
 (ctypes on libb200p2p.so), compared byte for byte with the oracle.
 
-One GPU means one rank, so the transfer is a self send/recv inside a group — the same fused
-kernel, flags, sequence rings and copy loops a peer transfer uses, with the "peer" mapping
+One GPU means one rank, so the transfer is a self send/recv inside a group.  Every test runs
+twice: as the engine does it by default (a matched self send/recv is one local copy, no flags)
+and with the "loopback" option, which sends the same bytes through the full wire protocol —
+eager ring, push with post/done flags, pull with adaptive receive — with the "peer" mapping
 pointing at local memory.  Cross-GPU runs are in test_gpu_multi.py.
 """
 import ctypes
@@ -16,15 +18,17 @@ SEED = 0x5EED0000
 CAP = 64 << 20
 
 
-@pytest.fixture(scope="module")
-def eng(p2p, oracle):
+@pytest.fixture(scope="module", params=["copy", "loopback"])
+def eng(request, p2p, oracle):
     import torch
     assert torch.cuda.is_available(), "gpu tests need a GPU"
     torch.cuda.set_device(0)
     p2p.init(0, 1, 0)
+    p2p.set_option("loopback", 1 if request.param == "loopback" else 0)
     src = p2p.DeviceBuffer(CAP + 4096)
     dst = p2p.DeviceBuffer(CAP + 4096)
     win = p2p.register(dst.ptr, dst.nbytes)
+    p2p.register(src.ptr, src.nbytes)      # lets large messages be pulled
     stream = torch.cuda.Stream()
 
     class E:
@@ -33,6 +37,7 @@ def eng(p2p, oracle):
     e = E()
     e.p2p, e.oracle, e.src, e.dst, e.win, e.stream, e.torch = p2p, oracle, src, dst, win, stream, torch
     e.iter = 0
+    e.loopback = request.param == "loopback"
     yield e
     p2p.set_option("path", p2p.PATH_AUTO)
     torch.cuda.synchronize()
@@ -80,16 +85,56 @@ def test_auto_path_sizes(eng, n):
     assert_exact(eng, n)
 
 
-@pytest.mark.parametrize("vec", [16, 32])
 @pytest.mark.parametrize("n", [16385, 65536, (1 << 20) + 3, (8 << 20) + 48, 32 << 20])
-def test_ldst_path(eng, n, vec):
+def test_ldst_push_path(eng, n):
     eng.p2p.set_option("path", eng.p2p.PATH_LDST)
-    eng.p2p.set_option("vec_bytes", vec)
+    eng.p2p.set_option("eager_bytes", 16384)     # one rank: the limit may shrink so that small pushes are exercised too
     try:
         assert eng.p2p.query_plan(n, 0)[0] == eng.p2p.PATH_LDST
         assert_exact(eng, n)
     finally:
-        eng.p2p.set_option("vec_bytes", 16)
+        eng.p2p.set_option("eager_bytes", 1 << 20)
+
+
+@pytest.mark.parametrize("n", [4 << 20, (4 << 20) + 1, (8 << 20) + 48, (32 << 20) - 5])
+@pytest.mark.parametrize("src_off,dst_off", [(0, 0), (16, 48), (3, 19), (5, 6)])
+def test_pull_path(eng, n, src_off, dst_off):
+    """At or above the pull threshold (4 MiB) the receiver loads the payload from the sender's
+    registered buffer.  (Only the loopback run exercises the wire protocol.)"""
+    eng.p2p.set_option("path", eng.p2p.PATH_AUTO)
+    eng.p2p.set_option("bidir_push", 0)   # sender and receiver are the same rank here; do not take that for a bidirectional exchange
+    try:
+        assert_exact(eng, n, src_off, dst_off)
+    finally:
+        eng.p2p.set_option("bidir_push", 1)
+
+
+def test_large_message_fallbacks(eng):
+    """Large message with only one side registered: unregistered sender -> it announces a push;
+    unregistered receiver -> pull still works; neither -> reported, not hung."""
+    p2p, torch = eng.p2p, eng.torch
+    p2p.set_option("path", p2p.PATH_AUTO)
+    p2p.set_option("bidir_push", 0)
+    n = (6 << 20) + 11
+    loose_src, loose_dst = p2p.DeviceBuffer(n), p2p.DeviceBuffer(n + 64)
+    try:
+        for src, dst, it in ((loose_src, eng.dst, 31), (eng.src, loose_dst, 32)):
+            p2p.pattern_fill(src.ptr, n, SEED, 0, it, eng.stream)
+            dst.tensor().fill_(0xA5)
+            torch.cuda.synchronize()
+            with p2p.group():
+                p2p.recv(dst.ptr, n, p2p.INT8, 0, eng.stream)
+                p2p.send(src.ptr, n, p2p.INT8, 0, eng.stream)
+            eng.stream.synchronize()
+            p2p.raise_async_error()
+            got = dst.tensor()[: n + 32].cpu().numpy()
+            assert np.array_equal(got[:n], eng.oracle.expected_recv(n, SEED, 0, it))
+            assert np.all(got[n:] == 0xA5)
+    finally:
+        p2p.set_option("bidir_push", 1)
+        torch.cuda.synchronize()
+        loose_src.free()
+        loose_dst.free()
 
 
 @pytest.mark.parametrize("chunk,stages", [(16384, 8), (32768, 4), (8192, 16), (65536, 3)])
@@ -97,6 +142,7 @@ def test_ldst_path(eng, n, vec):
 def test_tma_path(eng, n, chunk, stages):
     p2p = eng.p2p
     p2p.set_option("path", p2p.PATH_TMA)
+    p2p.set_option("eager_bytes", 16384)
     p2p.set_option("tma_stages", 2)
     p2p.set_option("tma_chunk", chunk)
     p2p.set_option("tma_stages", stages)
@@ -104,9 +150,10 @@ def test_tma_path(eng, n, chunk, stages):
         assert p2p.query_plan(n, 0)[0] == p2p.PATH_TMA
         assert_exact(eng, n)
     finally:
+        p2p.set_option("eager_bytes", 1 << 20)
         p2p.set_option("tma_stages", 2)
-        p2p.set_option("tma_chunk", 16384)
-        p2p.set_option("tma_stages", 8)
+        p2p.set_option("tma_chunk", 32768)
+        p2p.set_option("tma_stages", 6)
 
 
 @pytest.mark.parametrize("path", ["ldst", "tma", "auto"])
@@ -136,10 +183,10 @@ def test_cfg1_shape_64mib_float(eng):
 
 
 def test_sequence_rings_wrap(eng):
-    """More messages than ring slots on both protocols (64 rendezvous, 8 eager) without a host sync."""
+    """More messages than ring slots on both protocols (64 rendezvous, 4 eager) without a host sync."""
     p2p = eng.p2p
     p2p.set_option("path", p2p.PATH_AUTO)
-    for n, reps in ((64, 40), (100_000, 150)):
+    for n, reps in ((64, 40), (100_000, 40), ((1 << 20) + 4096, 150)):
         p2p.pattern_fill(eng.src.ptr, n, SEED, 0, 9000 + n, eng.stream)
         eng.dst.tensor().fill_(0xA5)
         eng.torch.cuda.synchronize()
@@ -228,16 +275,18 @@ def test_full_size_256mib_properties(eng, p2p, oracle):
 
 
 def test_unregistered_receive_buffer_is_refused(eng):
+    if not eng.loopback:
+        pytest.skip("a matched self send/recv is a local copy and needs no window")
     p2p = eng.p2p
-    other = p2p.DeviceBuffer(1 << 20)
+    other = p2p.DeviceBuffer(2 << 20)
     try:
         with pytest.raises(p2p.P2PError) as ei:
             with p2p.group():
-                p2p.recv(other.ptr, 1 << 20, p2p.INT8, 0, eng.stream)
-                p2p.send(eng.src.ptr, 1 << 20, p2p.INT8, 0, eng.stream)
+                p2p.recv(other.ptr, 2 << 20, p2p.INT8, 0, eng.stream)
+                p2p.send(eng.src.ptr, 2 << 20, p2p.INT8, 0, eng.stream)
         assert ei.value.code == p2p.INVALID_USAGE and "registered window" in str(ei.value)
         # nothing was enqueued and no sequence number moved: the next transfer still matches
-        assert_exact(eng, 1 << 20)
+        assert_exact(eng, 2 << 20)
         # eager-sized messages need no window
         it = 4321
         p2p.pattern_fill(eng.src.ptr, 1000, SEED, 0, it, eng.stream)
@@ -262,7 +311,7 @@ def test_argument_errors(eng):
     assert L.p2p_group_end() == p2p.INVALID_USAGE                                               # unbalanced
     assert L.p2p_init(0, 1, 0) == p2p.INVALID_USAGE                                             # twice
     assert L.p2p_set_option(b"nonsense", 1) == p2p.INVALID_ARGUMENT
-    assert L.p2p_set_option(b"vec_bytes", 24) == p2p.INVALID_ARGUMENT
+    assert L.p2p_set_option(b"tma_chunk", 100) == p2p.INVALID_ARGUMENT
     assert p2p.async_error() == p2p.SUCCESS
     assert_exact(eng, 4096)
 
@@ -278,11 +327,11 @@ import torch
 p2p = importlib.import_module("test-nccl-p2p_b200")
 torch.cuda.set_device(0)
 p2p.init(0, 1, 0)
-buf = p2p.DeviceBuffer(1 << 20)
+buf = p2p.DeviceBuffer(2 << 20)
 p2p.register(buf.ptr, buf.nbytes)
 p2p.set_option("timeout_ms", 200)
 s = torch.cuda.Stream()
-p2p.recv(buf.ptr, 1 << 20, p2p.INT8, 0, s)      # rendezvous receive, no matching send
+p2p.recv(buf.ptr, 2 << 20, p2p.INT8, 0, s)      # rendezvous receive, no matching send
 s.synchronize()
 assert p2p.async_error() == p2p.REMOTE_ERROR
 assert "never completed" in p2p.lib().p2p_get_last_error().decode()
