@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--size", type=int, default=256 << 20)
-    ap.add_argument("--no-extras", action="store_true", help="skip latency / all-pairs / NCCL side measurements")
+    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements (latency, all-pairs, NCCL in the same run, CPU baseline); used for profiling runs")
     return ap.parse_args()
 
 
@@ -321,7 +321,7 @@ def engine_arm(args):
     peaks, peak_kind = measured_peaks()
     if world == 1:
         roof = {"bound": "hbm", "achieved": round(2 * B / per_step / 1e9, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "peak_kind": f"{peak_kind} HBM copy (read+write bytes)", "traffic": TRAFFIC_PER_LAUNCH.get("local")}
+                "peak_kind": f"{peak_kind} HBM copy (read+write bytes)", "traffic": TRAFFIC_PER_LAUNCH.get("local") if B == (256 << 20) else None}
     else:
         roof = {"bound": "nvlink", "achieved": round(B / per_step / 1e9, 2), "peak": LINK_GBPS, "unit": "GB/s",
                 "peak_kind": f"nominal NVLink 5 per direction per GPU; measured peer copy on this pool {LINK_MEASURED_GBPS}",
@@ -353,7 +353,7 @@ def engine_arm(args):
             "roofline": roof,
             "parity": {"digest_before": f"{digest_before:#018x}", "digest_after": f"{digest_after:#018x}", "mismatches": 0},
         }
-        if world == 1:
+        if world == 1 and not args.no_extras:
             line["cpu_baseline"] = cpu_baseline(B)
         if extras:
             line["extras"] = extras
@@ -370,8 +370,10 @@ def engine_arm(args):
     return 0
 
 
-# dram bytes per launch from the committed ncu captures (profiles/); None until a capture exists
-TRAFFIC_PER_LAUNCH = {"local": None, "peer": None}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel, from the committed ncu --set full
+# capture of this same command at N=1 (profiles/r01_ncu/prof_local_tma.raw.csv: 268.49 MB read + 212.76 MB written,
+# the rest of the 268 MB written still sits in L2 when the kernel ends).  No ncu on multi-rank runs: null there.
+TRAFFIC_PER_LAUNCH = {"local": 481247232, "peer": None}
 
 
 def side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks):

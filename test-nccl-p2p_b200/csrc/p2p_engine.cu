@@ -87,7 +87,8 @@ struct Options {
     long long self_nblocks = 0;    // CTAs of a local copy, 0 auto
     long long pull_nblocks = 0;    // CTAs that pull a large message, 0 auto
     long long eager_nblocks = 0;   // most CTAs an eager message may use, 0 auto
-    long long eager_bytes = 1 << 20;   // measured on 2xB200: the eager ring beats the rendezvous push up to 1 MiB
+    long long eager_bytes = 512 << 10; // pairs: the eager ring beats the push up to 1 MiB (8.4 vs 14.5 us); all-pairs on 8 GPUs
+                                       // wants 1 MiB pushed (27.9 vs 41.9 us, NCCL 32.8): 512 KiB serves both
     long long pull_min_bytes = 4 << 20;  // messages at least this large let the receiver pull (-1: never); same on all ranks
     long long timeout_ms = 20000;
     long long tma_chunk = 32 * 1024;
@@ -237,7 +238,7 @@ inline int self_copy_flavour(size_t nbytes) {
 }
 
 // CTAs that move `nbytes`: `flavour` of the launch, destination class decides the cap
-inline int mover_ctas(size_t nbytes, int flavour, bool self, bool pull) {
+inline int mover_ctas(size_t nbytes, int flavour, bool self, bool pull, int fanout = 1) {
     if (flavour == FLAVOUR_TMA && !pull) {
         const size_t chunks = (nbytes + (size_t)g.opt.tma_chunk - 1) / (size_t)g.opt.tma_chunk;
         const long long cap = self ? (g.opt.self_nblocks ? g.opt.self_nblocks : (long long)g.sm_count * g.ctas_tma)
@@ -248,8 +249,10 @@ inline int mover_ctas(size_t nbytes, int flavour, bool self, bool pull) {
     const size_t tiles = (nbytes + tile - 1) / tile;
     long long cap;
     if (self) cap = g.opt.self_nblocks ? g.opt.self_nblocks : (long long)g.sm_count;  // 1 CTA per SM beat 2 (6.17 vs 6.02 TB/s)
-    else if (pull) cap = g.opt.pull_nblocks ? g.opt.pull_nblocks : 64;
-    else cap = g.opt.nblocks ? g.opt.nblocks : 32;
+    // one flow wants many CTAs in flight (pull: 64 -> 725 GB/s, 32 -> 610); several concurrent flows per GPU
+    // want few each (all-pairs on 8 GPUs: 8 CTAs per flow 4.83 TB/s, 32 per flow 4.58)
+    else if (pull) cap = g.opt.pull_nblocks ? g.opt.pull_nblocks : (fanout >= 3 ? 8 : fanout == 2 ? 32 : 64);
+    else cap = g.opt.nblocks ? g.opt.nblocks : (fanout >= 3 ? 8 : 32);
     return (int)std::max<size_t>(1, std::min<size_t>(tiles, (size_t)cap));
 }
 
@@ -295,6 +298,11 @@ int launch_pending() {
         }
     }
 
+    int n_large_sends = 0, n_large_recvs = 0;
+    for (size_t i = 0; i < ops.size(); ++i)
+        if (partner[i] < 0 && is_large(ops[i].nbytes) && (long long)ops[i].nbytes > g.opt.eager_bytes)
+            (ops[i].is_send ? n_large_sends : n_large_recvs)++;
+
     // validate everything before any sequence number moves
     struct Resolved { Proto proto; uint32_t win; uint64_t off; bool registered; bool pull_send; int nblocks; };
     std::vector<Resolved> res(ops.size());
@@ -323,13 +331,15 @@ int launch_pending() {
                         "sender and need p2p_register_export/import first",
                         op.buf, op.nbytes, g.opt.eager_bytes, g.opt.pull_min_bytes);
         if (op.is_send && r.proto == PROTO_LARGE) {
-            // the sender decides: let the receiver pull when it can map my buffer, unless this group also
-            // receives a large message from the same peer (both directions busy: pushes interfere less)
+            // The sender decides.  Let the receiver pull when it can map my buffer — except in a plain pairwise
+            // exchange (one large send, and a large receive from that same peer in the group), where two pushes
+            // interfere less than two pulls (1.32 vs 1.24 TB/s between two B200s).  With several large sends in
+            // the group (fan-out, all-pairs) pulls with few CTAs win again (4.83 vs 4.28 TB/s on 8 GPUs).
             bool also_receiving = false;
             for (size_t j = 0; j < ops.size(); ++j)
                 if (!ops[j].is_send && ops[j].peer == op.peer && partner[j] < 0 && is_large(ops[j].nbytes)) also_receiving = true;
-            if (!g.opt.bidir_push) also_receiving = false;
-            r.pull_send = r.registered && !also_receiving && g.opt.path != 2 && g.opt.path != 1;
+            const bool pairwise = also_receiving && n_large_sends == 1 && g.opt.bidir_push;
+            r.pull_send = r.registered && !pairwise && g.opt.path != 2 && g.opt.path != 1;
         }
         if (op.is_send && !(r.proto == PROTO_LARGE && r.pull_send) && push_flavour(op.nbytes) == 2) flavour = FLAVOUR_TMA;
     }
@@ -367,15 +377,28 @@ int launch_pending() {
                 only_small = false;
                 if (op.is_send) {
                     if (r.pull_send) ++n_ctrl;
-                    else { r.nblocks = mover_ctas(op.nbytes, flavour, self, false); want += r.nblocks; }
+                    else { r.nblocks = mover_ctas(op.nbytes, flavour, self, false, n_large_sends); want += r.nblocks; }
                 } else {
-                    r.nblocks = mover_ctas(op.nbytes, FLAVOUR_LDST, self, true);
+                    r.nblocks = mover_ctas(op.nbytes, FLAVOUR_LDST, self, true, n_large_recvs);
                     want += r.nblocks;
                 }
                 break;
         }
     }
-    budget -= fixed + (n_ctrl ? 1 : 0);
+    // Everything must be co-resident: roles wait for peers, and a CTA that cannot get an SM could keep a peer waiting
+    // for ever.  Eager roles may take at most half of the machine, movers share what is left.
+    budget -= (n_ctrl ? 1 : 0);
+    if (fixed > budget / 2) {
+        const long long room = std::max<long long>(budget / 2, 1);
+        long long now = 0;
+        for (size_t i = 0; i < ops.size(); ++i)
+            if (res[i].proto == PROTO_EAGER) {
+                res[i].nblocks = (int)std::max<long long>(1, res[i].nblocks * room / fixed);
+                now += res[i].nblocks;
+            }
+        fixed = now;
+    }
+    budget -= fixed;
     if (budget < 1) budget = 1;
     if (want > budget)
         for (size_t i = 0; i < ops.size(); ++i)
@@ -393,15 +416,15 @@ int launch_pending() {
 
     uint32_t next_block = n_ctrl ? 1 : 0;
     uint8_t* my = g.ctl;
-    // order of CTAs: control CTA, eager receives, eager sends, large receives (they start by waiting),
-    // then everything that pushes or copies
+    // order of CTAs: control CTA, eager sends (they wait for nothing that runs here), eager receives,
+    // large receives (they start by waiting), then everything that pushes or copies
     for (int pass = 0; pass < 5; ++pass) {
         for (size_t i = 0; i < ops.size(); ++i) {
             const PendingOp& op = ops[i];
             const Resolved& r = res[i];
             int cls;
             if (r.proto == PROTO_COPY) cls = op.is_send ? 4 : -1;
-            else if (r.proto == PROTO_EAGER) cls = op.is_send ? 2 : 1;
+            else if (r.proto == PROTO_EAGER) cls = op.is_send ? 1 : 2;
             else if (r.proto == PROTO_PUSH) cls = op.is_send ? 4 : 0;
             else cls = op.is_send ? (r.pull_send ? 0 : 4) : 3;
             if (cls != pass) continue;

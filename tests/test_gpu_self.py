@@ -76,7 +76,7 @@ def assert_exact(e, n, src_off=0, dst_off=0, **kw):
 
 
 SIZES = [0, 1, 7, 8, 9, 15, 16, 17, 31, 32, 33, 255, 4095, 4096, 4097, 16383, 16384, 16385, 65535, 65536, 65537,
-         (1 << 20) - 1, 1 << 20, (1 << 20) + 3, (4 << 20) + 16, 16 << 20]
+         (512 << 10) - 1, 512 << 10, (512 << 10) + 1, (1 << 20) - 1, 1 << 20, (1 << 20) + 3, (4 << 20) + 16, 16 << 20]
 
 
 @pytest.mark.parametrize("n", SIZES)
@@ -93,7 +93,7 @@ def test_ldst_push_path(eng, n):
         assert eng.p2p.query_plan(n, 0)[0] == eng.p2p.PATH_LDST
         assert_exact(eng, n)
     finally:
-        eng.p2p.set_option("eager_bytes", 1 << 20)
+        eng.p2p.set_option("eager_bytes", 512 << 10)
 
 
 @pytest.mark.parametrize("n", [4 << 20, (4 << 20) + 1, (8 << 20) + 48, (32 << 20) - 5])
@@ -150,7 +150,7 @@ def test_tma_path(eng, n, chunk, stages):
         assert p2p.query_plan(n, 0)[0] == p2p.PATH_TMA
         assert_exact(eng, n)
     finally:
-        p2p.set_option("eager_bytes", 1 << 20)
+        p2p.set_option("eager_bytes", 512 << 10)
         p2p.set_option("tma_stages", 2)
         p2p.set_option("tma_chunk", 32768)
         p2p.set_option("tma_stages", 6)
