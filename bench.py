@@ -286,7 +286,10 @@ def engine_arm(args):
     for _ in range(W):
         step()
     stream.synchronize()
+    launches0, ce0 = p2p.get_option("stat_launches"), p2p.get_option("stat_ce_copies")
     total = timed(step, K)
+    launches = p2p.get_option("stat_launches") - launches0      # kernels the engine launched in the timed region
+    ce_copies = p2p.get_option("stat_ce_copies") - ce0          # payloads it handed to the copy engine instead
     p2p.raise_async_error()
     digest_after = verify(2)
     per_step = total / K
@@ -328,6 +331,9 @@ def engine_arm(args):
                 "traffic": TRAFFIC_PER_LAUNCH.get("peer")}
     roof["frac"] = round(roof["achieved"] / roof["peak"], 4)
     roof["kernel"] = "p2p_group_kernel_tma" if plan[0] == p2p.PATH_TMA else "p2p_group_kernel_ldst"
+    if ce_copies:
+        roof["kernel"] = (f"copy engine (cudaMemcpyAsync to the peer mapping) for {ce_copies} of {K} payloads of this rank, "
+                          "between ce_wait_kernel / ce_signal_kernel; receives in p2p_group_kernel_ldst")
     roof["algorithmic_bytes_per_launch"] = (2 if world == 1 else 1) * B
     roof["ctas"] = plan[1]
 
@@ -349,7 +355,7 @@ def engine_arm(args):
             "clocks": clocks.summary(),
             "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": B * world, "d2h_bytes_per_step": B * world,
                     "steps": e2e_steps, "payload_intact": e2e_ok},
-            "gpu_launches": K * world,
+            "gpu_launches": launches * world,
             "roofline": roof,
             "parity": {"digest_before": f"{digest_before:#018x}", "digest_after": f"{digest_after:#018x}", "mismatches": 0},
         }

@@ -8,11 +8,17 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <cerrno>
 #include <cstring>
 #include <map>
 #include <mutex>
 #include <string>
 #include <vector>
+#include <atomic>
+#include <chrono>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <unistd.h>
 
 namespace p2p {
@@ -32,6 +38,7 @@ struct BootBlob {
     int64_t pull_min_bytes;
     uint64_t ctl_bytes;
     char pci_bus_id[32];
+    char hostbox_name[48];  // rank 0 only: POSIX shared-memory name of the host mailbox
     cudaIpcMemHandle_t ctl_handle;
 };
 static_assert(sizeof(BootBlob) <= kBlobBytes, "bootstrap blob too large");
@@ -58,6 +65,14 @@ struct PeerCtl {
     uint64_t pull_done[kRing];
     uint64_t ll_ack[kLLSlots];
     uint64_t pad[8];
+};
+
+// Host mailbox (POSIX shared memory, one per job): the receiver's HOST publishes where a large receive goes at the
+// moment p2p_recv is called, so that the sender's host can address a DMA copy.  It carries no ordering: readiness of
+// the buffer is still signalled on the device.  Entry [dst][src][seq % kRing], seqlock-protected.
+struct HostPost {
+    std::atomic<uint64_t> seq;
+    std::atomic<uint64_t> word;
 };
 
 struct Window {
@@ -99,6 +114,11 @@ struct Options {
                                    // measured faster), 2 every group (push/pull kernels measured slower with it)
     long long loopback = 0;        // 1: a send to oneself goes through the wire protocol instead of a plain copy (tests)
     long long bidir_push = 1;      // a large send whose group also receives a large message from that peer pushes
+    long long ce_min_bytes = -1;   // experimental, off: a send that is alone in its group and at least this large goes through
+                                   // the copy engine when the receiver's host has already said where to.  Measured on 2xB200
+                                   // it loses to the pull kernel (256 MiB: 708 vs 726 GB/s streamed, 496 vs 368 us per
+                                   // ping-pong hop): kernel -> DMA -> kernel on one stream costs more than the DMA gains.
+    long long ce_wait_us = 200;    // how long p2p_send's host side waits for that word before using the SM path
 };
 
 struct Engine {
@@ -128,6 +148,14 @@ struct Engine {
     void* pending_reg_buf = nullptr;
     size_t pending_reg_bytes = 0;
     bool has_pending_reg = false;
+
+    HostPost* hostbox = nullptr;  // [nranks][nranks][kRing]
+    size_t hostbox_bytes = 0;
+    char hostbox_name[48] = "";
+    cudaStream_t ce_stream[P2P_MAX_RANKS] = {};
+    cudaEvent_t ce_join[P2P_MAX_RANKS] = {};
+    cudaEvent_t ce_fork = nullptr;
+    long long stat_launches = 0, stat_ce_copies = 0;
 
     int group_depth = 0;
     std::vector<PendingOp> group_ops;
@@ -202,6 +230,70 @@ long long env_ll(const char* name, long long dflt) {
 int check_ready() {
     if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
     if (!g.connected) return fail(P2P_INVALID_USAGE, "p2p_connect has not been called");
+    return P2P_SUCCESS;
+}
+
+// ---- host mailbox ---------------------------------------------------------------------
+
+inline HostPost* hostbox_entry(int dst, int src, uint64_t seq) {
+    return g.hostbox + ((size_t)dst * g.nranks + src) * kRing + seq % kRing;
+}
+
+void hostbox_publish(int src, uint64_t seq, uint64_t word) {
+    if (!g.hostbox) return;
+    HostPost* e = hostbox_entry(g.rank, src, seq);
+    e->seq.store(0, std::memory_order_relaxed);  // seqlock: invalidate, write, validate
+    std::atomic_thread_fence(std::memory_order_release);
+    e->word.store(word, std::memory_order_relaxed);
+    e->seq.store(seq, std::memory_order_release);
+}
+
+// Has rank `dst` already said where message `seq` from me goes?  Waits at most `wait_us`.
+bool hostbox_lookup(int dst, uint64_t seq, long long wait_us, uint64_t* word) {
+    if (!g.hostbox) return false;
+    HostPost* e = hostbox_entry(dst, g.rank, seq);
+    const auto t0 = std::chrono::steady_clock::now();
+    for (;;) {
+        if (e->seq.load(std::memory_order_acquire) == seq) {
+            const uint64_t w = e->word.load(std::memory_order_relaxed);
+            std::atomic_thread_fence(std::memory_order_acquire);
+            if (e->seq.load(std::memory_order_relaxed) == seq) {
+                *word = w;
+                return true;
+            }
+        }
+        if (std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count() >= wait_us)
+            return false;
+    }
+}
+
+int hostbox_create() {
+    snprintf(g.hostbox_name, sizeof g.hostbox_name, "/b200p2p.%d.%llx", (int)getpid(),
+             (unsigned long long)std::chrono::steady_clock::now().time_since_epoch().count());
+    int fd = shm_open(g.hostbox_name, O_CREAT | O_EXCL | O_RDWR, 0600);
+    if (fd < 0) return fail(P2P_SYSTEM_ERROR, "shm_open(%s) failed: %s", g.hostbox_name, strerror(errno));
+    if (ftruncate(fd, (off_t)g.hostbox_bytes) != 0) {
+        close(fd);
+        shm_unlink(g.hostbox_name);
+        return fail(P2P_SYSTEM_ERROR, "ftruncate(%s, %zu) failed: %s", g.hostbox_name, g.hostbox_bytes, strerror(errno));
+    }
+    void* m = mmap(nullptr, g.hostbox_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (m == MAP_FAILED) {
+        shm_unlink(g.hostbox_name);
+        return fail(P2P_SYSTEM_ERROR, "mmap of the host mailbox failed: %s", strerror(errno));
+    }
+    g.hostbox = (HostPost*)m;  // fresh shared memory is zero-filled: no entry is valid
+    return P2P_SUCCESS;
+}
+
+int hostbox_open(const char* name) {
+    int fd = shm_open(name, O_RDWR, 0600);
+    if (fd < 0) return fail(P2P_SYSTEM_ERROR, "shm_open(%s) failed: %s (ranks must share /dev/shm)", name, strerror(errno));
+    void* m = mmap(nullptr, g.hostbox_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (m == MAP_FAILED) return fail(P2P_SYSTEM_ERROR, "mmap of the host mailbox failed: %s", strerror(errno));
+    g.hostbox = (HostPost*)m;
     return P2P_SUCCESS;
 }
 
@@ -304,7 +396,8 @@ int launch_pending() {
             (ops[i].is_send ? n_large_sends : n_large_recvs)++;
 
     // validate everything before any sequence number moves
-    struct Resolved { Proto proto; uint32_t win; uint64_t off; bool registered; bool pull_send; int nblocks; };
+    struct Resolved { Proto proto; uint32_t win; uint64_t off; bool registered; bool pull_send; int nblocks;
+                      uint64_t seq; bool ce; uint64_t ce_word; };
     std::vector<Resolved> res(ops.size());
     int flavour = FLAVOUR_LDST;
     size_t nops_out = 0;
@@ -346,6 +439,39 @@ int launch_pending() {
     if (nops_out > (size_t)kMaxGroupOps)
         return fail(P2P_INVALID_USAGE, "a group holds at most %d operations (got %zu)", kMaxGroupOps, nops_out);
 
+    // Sequence numbers in PROGRAM order (the k-th send to a peer pairs with its k-th receive, whatever protocol
+    // each message ends up using); nothing below this point can fail for a reason the peer would not share.
+    for (size_t i = 0; i < ops.size(); ++i) {
+        Resolved& r = res[i];
+        if (r.proto == PROTO_COPY) continue;
+        const int p = ops[i].peer;
+        if (r.proto == PROTO_EAGER) r.seq = ops[i].is_send ? ++g.ll_send_seq[p] : ++g.ll_recv_seq[p];
+        else r.seq = ops[i].is_send ? ++g.rdv_send_seq[p] : ++g.rdv_recv_seq[p];
+        // a large receive also tells the sender's HOST where it goes (copy-engine path)
+        if (!ops[i].is_send && r.proto == PROTO_LARGE && p != me)
+            hostbox_publish(p, r.seq, r.registered ? make_post_word(r.seq, r.win, r.off) : 0);
+    }
+    // Copy engine (opt-in) for a send that is alone in its group and whose destination the host already knows.
+    // Alone, because the chain runs beside the group's kernel on another stream and a receive in that kernel
+    // may depend on it: two launches that must overlap are not something a GPU promises.  Never waits longer
+    // than ce_wait_us for the receiver's host; otherwise the SM path is used as if the option were off.
+    bool any_ce = false;
+    for (size_t i = 0; i < ops.size(); ++i) {
+        Resolved& r = res[i];
+        const PendingOp& op = ops[i];
+        if (!(op.is_send && r.proto == PROTO_LARGE && op.peer != me)) continue;
+        if (g.opt.ce_min_bytes < 0 || (long long)op.nbytes < g.opt.ce_min_bytes || ops.size() != 1) continue;
+        if (g.opt.path != 0 && g.opt.path != 3) continue;
+        uint64_t word = 0;
+        if (!hostbox_lookup(op.peer, r.seq, g.opt.ce_wait_us, &word) || word == 0) continue;
+        const uint32_t win = (uint32_t)(word >> 40) & 0xffu;
+        if (win >= P2P_MAX_WINDOWS || !g.windows[win].used || !g.windows[win].peer_base[op.peer]) continue;
+        r.ce = true;
+        r.ce_word = word;
+        r.pull_send = false;
+        any_ce = true;
+    }
+
     // CTA counts
     const int per_sm = flavour == FLAVOUR_TMA ? g.ctas_tma : g.ctas_ldst;
     long long budget = (long long)g.sm_count * per_sm;
@@ -376,6 +502,7 @@ int launch_pending() {
             case PROTO_LARGE:
                 only_small = false;
                 if (op.is_send) {
+                    if (r.ce) break;  // moved by the copy engine, outside the kernel
                     if (r.pull_send) ++n_ctrl;
                     else { r.nblocks = mover_ctas(op.nbytes, flavour, self, false, n_large_sends); want += r.nblocks; }
                 } else {
@@ -426,7 +553,7 @@ int launch_pending() {
             if (r.proto == PROTO_COPY) cls = op.is_send ? 4 : -1;
             else if (r.proto == PROTO_EAGER) cls = op.is_send ? 1 : 2;
             else if (r.proto == PROTO_PUSH) cls = op.is_send ? 4 : 0;
-            else cls = op.is_send ? (r.pull_send ? 0 : 4) : 3;
+            else cls = op.is_send ? (r.ce ? -1 : r.pull_send ? 0 : 4) : 3;
             if (cls != pass) continue;
             OpDesc& d = args.ops[args.h.nops++];
             const int p = op.peer;
@@ -439,20 +566,20 @@ int launch_pending() {
                 d.kind = OP_COPY;
                 d.aux = (uint64_t)ops[(size_t)partner[i]].buf;
             } else if (r.proto == PROTO_EAGER && !op.is_send) {
-                const uint64_t seq = ++g.ll_recv_seq[p];
+                const uint64_t seq = r.seq;
                 d.kind = OP_RECV_LL;
                 d.seq = seq;
                 d.aux = (uint64_t)ll_slot(my, p, seq);
                 d.f_signal = (uint64_t)&peer_section(theirs, me)->ll_ack[seq % kLLSlots];
                 d.arrive = (uint64_t)arrive_ll(p, seq);
             } else if (r.proto == PROTO_EAGER) {
-                const uint64_t seq = ++g.ll_send_seq[p];
+                const uint64_t seq = r.seq;
                 d.kind = OP_SEND_LL;
                 d.seq = seq;
                 d.aux = (uint64_t)ll_slot(theirs, me, seq);
                 d.f_wait = (uint64_t)&peer_section(my, p)->ll_ack[seq % kLLSlots];
             } else if (!op.is_send) {
-                const uint64_t seq = ++g.rdv_recv_seq[p];
+                const uint64_t seq = r.seq;
                 d.seq = seq;
                 // what a pushing sender needs from me
                 d.word = r.registered ? make_post_word(seq, r.win, r.off) : 0;
@@ -468,7 +595,7 @@ int launch_pending() {
                     d.arrive = (uint64_t)arrive_pull(p, seq);
                 }
             } else {
-                const uint64_t seq = ++g.rdv_send_seq[p];
+                const uint64_t seq = r.seq;
                 d.seq = seq;
                 if (r.proto == PROTO_LARGE && r.pull_send) {
                     d.kind = OP_POST;  // publish where my payload lies, wait until it has been read
@@ -494,13 +621,13 @@ int launch_pending() {
         }
     }
     const uint32_t grid = next_block;
-    if (grid == 0) return P2P_SUCCESS;
+    if (grid == 0 && !any_ce) return P2P_SUCCESS;
     bool light = true;  // no rendezvous role in the group
     for (uint32_t i = 0; i < args.h.nops; ++i) {
         const uint32_t k = args.ops[i].kind;
         if (k == OP_POST || k == OP_PUSH || k == OP_RECV_ADAPT) light = false;
     }
-    args.h.pdl = (g.opt.pdl == 2 || (g.opt.pdl == 1 && light)) ? 1 : 0;
+    args.h.pdl = (g.opt.pdl == 2 || (g.opt.pdl == 1 && light && !any_ce)) ? 1 : 0;
     // small eager-only groups run with 128-thread CTAs: less to launch on the latency path
     const uint32_t block = (flavour == FLAVOUR_LDST && only_small && eager_total <= 8192) ? 128 : kLdstThreads;
 
@@ -519,8 +646,38 @@ int launch_pending() {
         CUDA_TRY(cudaEventRecord(g.ev_pool[i], others[i]));
         CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ev_pool[i], 0));
     }
-    const int dyn_smem = flavour == FLAVOUR_TMA ? (int)(g.opt.tma_chunk * g.opt.tma_stages) : 0;
-    CUDA_TRY(launch_group(flavour, args, grid, block, dyn_smem, launch_stream));
+    // copy-engine chains fork off BEFORE the kernel: the kernel may hold a receive that only completes once
+    // the peer's chain has run, and the peer's chain may need ours
+    if (any_ce) CUDA_TRY(cudaEventRecord(g.ce_fork, launch_stream));
+    if (grid > 0) {
+        const int dyn_smem = flavour == FLAVOUR_TMA ? (int)(g.opt.tma_chunk * g.opt.tma_stages) : 0;
+        CUDA_TRY(launch_group(flavour, args, grid, block, dyn_smem, launch_stream));
+        g.stat_launches++;
+    }
+    if (any_ce) {
+        for (size_t i = 0; i < ops.size(); ++i) {
+            if (!res[i].ce) continue;
+            const PendingOp& op = ops[i];
+            const int p = op.peer;
+            const uint64_t seq = res[i].seq, word = res[i].ce_word;
+            if (!g.ce_stream[p]) {
+                CUDA_TRY(cudaStreamCreateWithFlags(&g.ce_stream[p], cudaStreamNonBlocking));
+                CUDA_TRY(cudaEventCreateWithFlags(&g.ce_join[p], cudaEventDisableTiming));
+            }
+            uint8_t* theirs = g.peer_ctl[p];
+            uint8_t* dst = g.windows[(word >> 40) & 0xffu].peer_base[p] + (word & kPostOffMask);
+            cudaStream_t cs = g.ce_stream[p];
+            CUDA_TRY(cudaStreamWaitEvent(cs, g.ce_fork, 0));
+            CUDA_TRY(launch_ce_wait(&peer_section(theirs, me)->pull_post[seq % kRing], make_post_word(seq, kWinPushPlease, 0),
+                                    &peer_section(my, p)->post[seq % kRing], seq, word, args.h, cs));
+            CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
+            CUDA_TRY(launch_ce_signal(&peer_section(theirs, me)->done[seq % kRing], seq, cs));
+            CUDA_TRY(cudaEventRecord(g.ce_join[p], cs));
+            CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ce_join[p], 0));
+            g.stat_launches += 2;
+            g.stat_ce_copies++;
+        }
+    }
     if (!others.empty()) {
         CUDA_TRY(cudaEventRecord(g.ev_done, launch_stream));
         for (cudaStream_t s : others) CUDA_TRY(cudaStreamWaitEvent(s, g.ev_done, 0));
@@ -639,6 +796,8 @@ int p2p_init(int rank, int nranks, int device) {
     o.pdl = env_ll("P2P_PDL", o.pdl);
     o.loopback = env_ll("P2P_LOOPBACK", o.loopback);
     o.bidir_push = env_ll("P2P_BIDIR_PUSH", o.bidir_push);
+    o.ce_min_bytes = env_ll("P2P_CE_MIN_BYTES", o.ce_min_bytes);
+    o.ce_wait_us = env_ll("P2P_CE_WAIT_US", o.ce_wait_us);
     o.tma_chunk = env_ll("P2P_TMA_CHUNK", o.tma_chunk);
     o.tma_stages = env_ll("P2P_TMA_STAGES", o.tma_stages);
     o.tma_min_bytes = env_ll("P2P_TMA_MIN_BYTES", o.tma_min_bytes);
@@ -674,6 +833,15 @@ int p2p_init(int rank, int nranks, int device) {
     if (g.ctas_tma < 1) g.ctas_tma = 1;
     CUDA_TRY(cudaDeviceSynchronize());
     g.peer_ctl[rank] = g.ctl;
+    g.hostbox = nullptr;
+    g.hostbox_name[0] = '\0';
+    g.hostbox_bytes = sizeof(HostPost) * (size_t)nranks * nranks * kRing;
+    if (nranks > 1 && rank == 0) {
+        int rc = hostbox_create();
+        if (rc) return rc;
+    }
+    CUDA_TRY(cudaEventCreateWithFlags(&g.ce_fork, cudaEventDisableTiming));
+    g.stat_launches = g.stat_ce_copies = 0;
     g.inited = true;
     g.connected = false;
     return P2P_SUCCESS;
@@ -700,6 +868,7 @@ int p2p_export(void* blob) {
     b.pull_min_bytes = g.opt.pull_min_bytes;
     b.ctl_bytes = g.ctl_bytes;
     CUDA_TRY(cudaDeviceGetPCIBusId(b.pci_bus_id, sizeof b.pci_bus_id, g.device));
+    memcpy(b.hostbox_name, g.hostbox_name, sizeof b.hostbox_name);
     if (g.nranks > 1) CUDA_TRY(cudaIpcGetMemHandle(&b.ctl_handle, g.ctl));
     memcpy(blob, &b, sizeof b);
     return P2P_SUCCESS;
@@ -742,6 +911,13 @@ int p2p_connect(const void* all_blobs) {
                         r, b.pid, b.pci_bus_id, cudaGetErrorString(e));
         g.peer_ctl[r] = (uint8_t*)p;
     }
+    if (g.nranks > 1 && !g.hostbox) {
+        BootBlob b0;
+        memcpy(&b0, all_blobs, sizeof b0);
+        b0.hostbox_name[sizeof b0.hostbox_name - 1] = '\0';
+        // without it only the copy-engine path is lost; every other path works
+        if (b0.hostbox_name[0] && hostbox_open(b0.hostbox_name) != P2P_SUCCESS) g.hostbox = nullptr;
+    }
     g.connected = true;
     return P2P_SUCCESS;
 }
@@ -764,6 +940,18 @@ int p2p_finalize(void) {
         g.peer_ctl[r] = nullptr;
         g.rdv_send_seq[r] = g.rdv_recv_seq[r] = g.ll_send_seq[r] = g.ll_recv_seq[r] = 0;
     }
+    if (g.hostbox) munmap(g.hostbox, g.hostbox_bytes);
+    g.hostbox = nullptr;
+    if (g.rank == 0 && g.hostbox_name[0]) shm_unlink(g.hostbox_name);
+    g.hostbox_name[0] = '\0';
+    for (int r = 0; r < P2P_MAX_RANKS; ++r) {
+        if (g.ce_stream[r]) cudaStreamDestroy(g.ce_stream[r]);
+        if (g.ce_join[r]) cudaEventDestroy(g.ce_join[r]);
+        g.ce_stream[r] = nullptr;
+        g.ce_join[r] = nullptr;
+    }
+    if (g.ce_fork) cudaEventDestroy(g.ce_fork);
+    g.ce_fork = nullptr;
     cudaFree(g.ctl);
     cudaFree(g.arrive);
     cudaFree(g.win_table);
@@ -964,6 +1152,8 @@ static long long* option_slot(const char* name) {
     if (!strcmp(name, "pdl")) return &o.pdl;
     if (!strcmp(name, "loopback")) return &o.loopback;
     if (!strcmp(name, "bidir_push")) return &o.bidir_push;
+    if (!strcmp(name, "ce_min_bytes")) return &o.ce_min_bytes;
+    if (!strcmp(name, "ce_wait_us")) return &o.ce_wait_us;
     if (!strcmp(name, "tma_chunk")) return &o.tma_chunk;
     if (!strcmp(name, "tma_stages")) return &o.tma_stages;
     if (!strcmp(name, "tma_min_bytes")) return &o.tma_min_bytes;
@@ -997,7 +1187,7 @@ int p2p_set_option(const char* name, long long value) {
         int n = 1;
         if (occupancy(FLAVOUR_TMA, (int)(g.opt.tma_chunk * g.opt.tma_stages), &n) == cudaSuccess && n >= 1) g.ctas_tma = n;
         return P2P_SUCCESS;
-    } else if (value < 0 && strcmp(name, "tma_min_bytes") && strcmp(name, "self_tma_min_bytes")) {
+    } else if (value < 0 && strcmp(name, "tma_min_bytes") && strcmp(name, "self_tma_min_bytes") && strcmp(name, "ce_min_bytes")) {
         return fail(P2P_INVALID_ARGUMENT, "option '%s' must be >= 0", name);
     }
     *slot = value;
@@ -1009,6 +1199,8 @@ int p2p_get_option(const char* name, long long* value) {
     if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
     if (!name || !value) return fail(P2P_INVALID_ARGUMENT, "null argument");
     if (!strcmp(name, "sm_count")) { *value = g.sm_count; return P2P_SUCCESS; }
+    if (!strcmp(name, "stat_launches")) { *value = g.stat_launches; return P2P_SUCCESS; }
+    if (!strcmp(name, "stat_ce_copies")) { *value = g.stat_ce_copies; return P2P_SUCCESS; }
     if (!strcmp(name, "ctas_per_sm_ldst")) { *value = g.ctas_ldst; return P2P_SUCCESS; }
     if (!strcmp(name, "ctas_per_sm_tma")) { *value = g.ctas_tma; return P2P_SUCCESS; }
     long long* slot = option_slot(name);

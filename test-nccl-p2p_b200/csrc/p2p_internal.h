@@ -48,6 +48,9 @@ int set_last_error(int code, const char* fmt, ...);
 cudaError_t configure_kernels(int max_tma_smem);
 cudaError_t occupancy(int flavour, int dyn_smem, int* ctas_per_sm);
 cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, uint32_t block, int dyn_smem, cudaStream_t stream);
+cudaError_t launch_ce_wait(uint64_t* notice_flag, uint64_t notice_word, const uint64_t* post_slot, uint64_t seq,
+                           uint64_t expect_word, const GroupHdr& h, cudaStream_t stream);
+cudaError_t launch_ce_signal(uint64_t* done_flag, uint64_t seq, cudaStream_t stream);
 uint32_t pattern_grid(size_t nbytes, int sm_count);
 cudaError_t launch_pattern_fill(void* buf, size_t nbytes, uint64_t key, int sm_count, cudaStream_t stream);
 cudaError_t launch_pattern_check(const void* buf, size_t nbytes, uint64_t key, int check, int sm_count,

@@ -26,10 +26,12 @@ def matrix(n, *args, env=None, timeout=600):
     return run([MPIRUN, "-n", str(n), P2P_MATRIX, *args], timeout=timeout, env=env).stdout
 
 
-@pytest.mark.parametrize("path", ["auto", "ldst", "tma"])
+@pytest.mark.parametrize("path", ["auto", "ldst", "tma", "ce"])
 @pytest.mark.parametrize("n", RANKS)
 def test_reference_loops_verified(built, n, path):
-    out = matrix(n, "--size", "8M", "--iters", "4", "--verify", env={"P2P_PATH": path})
+    # "ce": opt in to the copy-engine path for the one-way loop (a send alone in its group); off by default
+    env = {"P2P_PATH": "auto", "P2P_CE_MIN_BYTES": "4194304", "P2P_CE_WAIT_US": "20000"} if path == "ce" else {"P2P_PATH": path}
+    out = matrix(n, "--size", "8M", "--iters", "4", "--verify", env=env)
     assert "verify: OK" in out and "VERIFY FAILED" not in out
     assert "Evaluating the Uni-Directional NCCL P2P Bandwidth (Gbps)" in out
     assert "Evaluating the Bi-Directional NCCL P2P Bandwidth (Gbps)" in out
