@@ -135,6 +135,15 @@ P2P_API int p2p_recv(void* buf, size_t count, int dtype, int peer, p2p_stream_t 
 P2P_API int p2p_group_start(void);
 P2P_API int p2p_group_end(void);
 
+/* ---- all-to-all on top of the all-pairs mode.  Block p of `sendbuf`
+ *      (count elements) goes to rank p, block p of `recvbuf` arrives from rank p; the block for
+ *      this rank itself is a local copy.  It is what NCCL users write as a grouped loop of
+ *      ncclSend/ncclRecv over all peers (nccl.h:438-440, 455-457) — the reference's own
+ *      bidirectional call shape (p2p_matrix.cc:212-228) widened from one peer to all — issued as
+ *      ONE group, hence one fused kernel launch.  Same window rules as p2p_send/p2p_recv:
+ *      register both buffers. ---- */
+P2P_API int p2p_alltoall(const void* sendbuf, void* recvbuf, size_t count, int dtype, p2p_stream_t stream);
+
 /* ---- errors: ncclGetErrorString / ncclGetLastError / ncclCommGetAsyncError
  *      (nccl.h:215,219,227) ---- */
 P2P_API const char* p2p_get_error_string(int result);

@@ -43,6 +43,17 @@ struct NcclBackend {
     }
     void group_start() { NCCLCHECK(ncclGroupStart()); }  // p2p_matrix.cc:212
     void group_end() { NCCLCHECK(ncclGroupEnd()); }      // p2p_matrix.cc:227
+    int nranks = 0;
+    // the grouped send/recv loop NCCL's documentation prescribes for all-to-all (nccl.h:438-440)
+    void alltoall(const void* send, void* recv, size_t bytes, cudaStream_t s) {
+        if (!nranks) NCCLCHECK(ncclCommCount(comm, &nranks));
+        NCCLCHECK(ncclGroupStart());
+        for (int p = 0; p < nranks; ++p) {
+            NCCLCHECK(ncclRecv((uint8_t*)recv + (size_t)p * bytes, bytes, ncclInt8, p, comm, s));
+            NCCLCHECK(ncclSend((const uint8_t*)send + (size_t)p * bytes, bytes, ncclInt8, p, comm, s));
+        }
+        NCCLCHECK(ncclGroupEnd());
+    }
 
     void fill(void* buf, size_t bytes, uint64_t seed, int r, uint64_t iter, cudaStream_t s) {
         host.resize(bytes);

@@ -53,6 +53,18 @@ def expected_recv(n: int, seed: int, src_rank: int, it: int) -> np.ndarray:
     return pattern_bytes(n, seed, src_rank, it)
 
 
+def alltoall_send(block: int, seed: int, rank: int, nranks: int) -> np.ndarray:
+    """What rank `rank` puts in its all-to-all send buffer: block p is the payload (seed, rank, iter=p)."""
+    return np.concatenate([pattern_bytes(block, seed, rank, p) for p in range(nranks)]) if block else np.zeros(0, np.uint8)
+
+
+def expected_alltoall_recv(block: int, seed: int, rank: int, nranks: int) -> np.ndarray:
+    """All-to-all law, i.e. the transfer law per peer: block p of rank `rank`'s receive buffer is block
+    `rank` of rank p's send buffer.  (What a grouped ncclSend/ncclRecv loop over all peers leaves,
+    nccl.h:438-440; p2p_matrix.cc:212-228 is the one-peer case.)"""
+    return np.concatenate([pattern_bytes(block, seed, p, rank) for p in range(nranks)]) if block else np.zeros(0, np.uint8)
+
+
 def mismatches(buf: np.ndarray, seed: int, rank: int, it: int):
     """(number of differing bytes, offset of the first one or len(buf))."""
     buf = np.asarray(buf, dtype=np.uint8).ravel()

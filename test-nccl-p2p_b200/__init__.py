@@ -33,7 +33,7 @@ PATH_AUTO, PATH_LDST, PATH_TMA, PATH_CE, PATH_EAGER, PATH_PULL = 0, 1, 2, 3, 4, 
 SYMBOLS = [
     "p2p_init", "p2p_blob_bytes", "p2p_export", "p2p_connect", "p2p_finalize", "p2p_rank", "p2p_nranks",
     "p2p_register_blob_bytes", "p2p_register_export", "p2p_register_import", "p2p_deregister",
-    "p2p_mem_alloc", "p2p_mem_free", "p2p_send", "p2p_recv", "p2p_group_start", "p2p_group_end",
+    "p2p_mem_alloc", "p2p_mem_free", "p2p_send", "p2p_recv", "p2p_group_start", "p2p_group_end", "p2p_alltoall",
     "p2p_get_error_string", "p2p_get_last_error", "p2p_get_async_error", "p2p_set_option", "p2p_get_option",
     "p2p_query_plan", "p2p_pattern_fill", "p2p_pattern_check", "p2p_digest", "p2p_digest_noalloc",
 ]
@@ -77,6 +77,7 @@ def lib() -> ctypes.CDLL:
         "p2p_mem_free": (i32, [vp]),
         "p2p_send": (i32, [vp, sz, i32, i32, vp]),
         "p2p_recv": (i32, [vp, sz, i32, i32, vp]),
+        "p2p_alltoall": (i32, [vp, vp, sz, i32, vp]),
         "p2p_group_start": (i32, []),
         "p2p_group_end": (i32, []),
         "p2p_get_error_string": (ctypes.c_char_p, [i32]),
@@ -196,6 +197,11 @@ def send(ptr: int, count: int, dtype: int, peer: int, stream=None) -> None:
 
 def recv(ptr: int, count: int, dtype: int, peer: int, stream=None) -> None:
     check(lib().p2p_recv(ctypes.c_void_p(ptr), count, dtype, peer, _stream_ptr(stream)))
+
+
+def alltoall(send_ptr: int, recv_ptr: int, count: int, dtype: int, stream=None) -> None:
+    """Block p of the send buffer to rank p, block p of the receive buffer from rank p; one fused launch."""
+    check(lib().p2p_alltoall(ctypes.c_void_p(send_ptr), ctypes.c_void_p(recv_ptr), count, dtype, _stream_ptr(stream)))
 
 
 def group_start() -> None:

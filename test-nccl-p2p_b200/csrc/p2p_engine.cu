@@ -1089,6 +1089,31 @@ int p2p_recv(void* buf, size_t count, int dtype, int peer, p2p_stream_t stream) 
     return enqueue(false, buf, count, dtype, peer, (cudaStream_t)stream);
 }
 
+int p2p_alltoall(const void* sendbuf, void* recvbuf, size_t count, int dtype, p2p_stream_t stream) {
+    int rc = check_ready();
+    if (rc) return rc;
+    if (dtype < 0 || dtype >= P2P_NUM_TYPES) return fail(P2P_INVALID_ARGUMENT, "unknown datatype %d", dtype);
+    const size_t es = kDtypeSize[dtype];
+    if (count > SIZE_MAX / es / (size_t)g.nranks) return fail(P2P_INVALID_ARGUMENT, "count %zu overflows size_t", count);
+    const size_t block = count * es;
+    if (block && (!sendbuf || !recvbuf)) return fail(P2P_INVALID_ARGUMENT, "null buffer with count %zu", count);
+    if (2 * g.nranks - 1 > kMaxGroupOps) return fail(P2P_INVALID_USAGE, "all-to-all over %d ranks needs more than %d operations in a group", g.nranks, kMaxGroupOps);
+    rc = p2p_group_start();
+    if (rc) return rc;
+    for (int p = 0; p < g.nranks && rc == P2P_SUCCESS; ++p) {
+        rc = enqueue(false, (uint8_t*)recvbuf + (size_t)p * block, count, dtype, p, (cudaStream_t)stream);
+        if (rc == P2P_SUCCESS) rc = enqueue(true, (const uint8_t*)sendbuf + (size_t)p * block, count, dtype, p, (cudaStream_t)stream);
+    }
+    if (rc != P2P_SUCCESS) {
+        // drop what was queued and close the group without launching anything
+        std::lock_guard<std::mutex> lk(g.mu);
+        g.group_ops.clear();
+        g.group_depth = 0;
+        return rc;
+    }
+    return p2p_group_end();
+}
+
 int p2p_group_start(void) {
     std::lock_guard<std::mutex> lk(g.mu);
     int rc = check_ready();

@@ -132,7 +132,7 @@ inline void usage(const char* prog, const char* backend) {
            "  --size BYTES[K|M|G]   message size (default 32M)\n"
            "  --iters N             timed iterations per cell (default 128)\n"
            "  --warmup N            untimed iterations per cell (default 0 for --timing ref, 20 for dev)\n"
-           "  --mode M              ref | uni | bidir | allpairs | ring | sweep | latency | local\n"
+           "  --mode M              ref | uni | bidir | allpairs | alltoall | ring | sweep | latency | local\n"
            "  --timing T            ref (rank-0 wall clock, sync per message) | dev (cudaEvents, back to back)\n"
            "  --verify              patterned payload, byte-exact check of every cell's receive buffer\n"
            "  --extra               also print GB/s, us per message and %% of 900 GB/s tables\n"
@@ -194,6 +194,7 @@ inline Options parse_args(int argc, char** argv, int rank, const char* backend) 
 //   void send(const void* buf, size_t bytes, int peer, cudaStream_t s);
 //   void recv(void* buf, size_t bytes, int peer, cudaStream_t s);
 //   void group_start(); void group_end();
+//   void alltoall(const void* send, void* recv, size_t bytes_per_rank, cudaStream_t s);
 //   void fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s);
 //   uint64_t check(const void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s,
 //                  uint64_t* digest);                            // mismatching bytes
@@ -203,18 +204,19 @@ class Driver {
 public:
     Driver(Backend& be, const Options& opt, int rank, int size) : be_(be), o_(opt), rank_(rank), size_(size) {}
 
-    void setup(size_t max_bytes, int recv_slots) {
+    void setup(size_t max_bytes, int recv_slots, int send_slots = 1) {
         CUDACHECK(cudaStreamCreateWithFlags(&s0_, cudaStreamNonBlocking));  // p2p_matrix.cc:121-122
         CUDACHECK(cudaStreamCreateWithFlags(&s1_, cudaStreamNonBlocking));
         cap_ = max_bytes ? max_bytes : 1;
         slots_ = recv_slots < 1 ? 1 : recv_slots;
-        CUDACHECK(cudaMalloc(&send_, cap_));                                // p2p_matrix.cc:127-130
+        send_cap_ = cap_ * (size_t)(send_slots < 1 ? 1 : send_slots);
+        CUDACHECK(cudaMalloc(&send_, send_cap_));                           // p2p_matrix.cc:127-130
         recv_cap_ = cap_ * (size_t)slots_ + 256;  // slack: --verify keeps a poisoned guard zone after the payload
         CUDACHECK(cudaMalloc(&recv_, recv_cap_));
-        CUDACHECK(cudaMemset(send_, 0, cap_));
+        CUDACHECK(cudaMemset(send_, 0, send_cap_));
         CUDACHECK(cudaMemset(recv_, 0, recv_cap_));
         CUDACHECK(cudaDeviceSynchronize());
-        be_.buffers(send_, cap_, recv_, recv_cap_);
+        be_.buffers(send_, send_cap_, recv_, recv_cap_);
         for (auto& evt : ev_) CUDACHECK(cudaEventCreate(&evt));
         if (!o_.json.empty() && rank_ == 0) {
             json_ = fopen(o_.json.c_str(), "w");
@@ -430,6 +432,64 @@ public:
             fflush(stdout);
         }
         record("allpairs", -1, -1, bytes, t, flows);
+    }
+
+    // ---- all-to-all: block p of the send buffer to rank p, block p of the receive buffer from rank p
+    // (the all-pairs mode with distinct payloads and the local block included)
+    void run_alltoall() {
+        const size_t bytes = o_.size;
+        auto round = [&](bool sync) {
+            be_.alltoall(send_, recv_, bytes, s0_);
+            if (sync) CUDACHECK(cudaStreamSynchronize(s0_));
+        };
+        unsigned long long bad_total = 0;
+        if (o_.verify) {
+            for (int p = 0; p < size_; ++p) be_.fill((uint8_t*)send_ + (size_t)p * bytes, bytes, o_.seed, rank_, (uint64_t)p, s0_);
+            CUDACHECK(cudaMemsetAsync(recv_, 0xA5, recv_cap_, s0_));
+            CUDACHECK(cudaStreamSynchronize(s0_));
+            MPI_Barrier(MPI_COMM_WORLD);
+            round(true);
+            uint64_t bad = 0, digest;
+            for (int p = 0; p < size_; ++p)
+                bad += be_.check((uint8_t*)recv_ + (size_t)p * bytes, bytes, o_.seed, p, (uint64_t)rank_, s0_, &digest);
+            uint8_t guard[64];
+            CUDACHECK(cudaMemcpy(guard, (uint8_t*)recv_ + (size_t)size_ * bytes, sizeof guard, cudaMemcpyDeviceToHost));
+            for (uint8_t gb : guard) if (gb != 0xA5) ++bad;
+            unsigned long long b = bad;
+            MPICHECK(MPI_Allreduce(&b, &bad_total, 1, MPI_UINT64_T, MPI_SUM, MPI_COMM_WORLD));
+            verified_cells_ += (uint64_t)size_ * size_;
+            verified_bytes_ += (uint64_t)size_ * size_ * bytes;
+            verify_failures_ += bad_total;
+        }
+        for (int i = 0; i < std::max(o_.warmup, 1); ++i) round(true);
+        double t;
+        MPI_Barrier(MPI_COMM_WORLD);
+        if (o_.timing == "dev") {
+            CUDACHECK(cudaEventRecord(ev_[0], s0_));
+            for (int i = 0; i < o_.iters; ++i) round(false);
+            CUDACHECK(cudaEventRecord(ev_[1], s0_));
+            CUDACHECK(cudaStreamSynchronize(s0_));
+            float ms;
+            CUDACHECK(cudaEventElapsedTime(&ms, ev_[0], ev_[1]));
+            double mine = ms * 1e-3 / o_.iters;
+            MPICHECK(MPI_Allreduce(&mine, &t, 1, MPI_DOUBLE, MPI_MAX, MPI_COMM_WORLD));
+        } else {
+            auto start = std::chrono::system_clock::now();
+            for (int i = 0; i < o_.iters; ++i) round(true);
+            MPI_Barrier(MPI_COMM_WORLD);
+            std::chrono::duration<double> el = std::chrono::system_clock::now() - start;
+            t = el.count() / o_.iters;
+            MPICHECK(MPI_Bcast(&t, 1, MPI_DOUBLE, 0, MPI_COMM_WORLD));
+        }
+        const double flows = (double)size_ * (size_ - 1);  // blocks that cross NVLink
+        if (rank_ == 0) {
+            printf("All-to-all (%s, timing %s): %d ranks, %zu bytes per block\n", be_.name(), o_.timing.c_str(), size_, bytes);
+            printf("  round %.2f us   aggregate over NVLink %.2f GB/s   per-GPU egress %.2f GB/s%s\n", t * 1e6,
+                   flows * bytes / t / 1e9, flows * bytes / t / 1e9 / size_,
+                   o_.verify ? (bad_total ? "   VERIFY FAILED" : "   verify OK") : "");
+            fflush(stdout);
+        }
+        record("alltoall", -1, -1, bytes, t, flows > 0 ? flows : 1.0);
     }
 
     // ---- ring: every rank sends `bytes` to (rank+1)%N and receives from (rank-1)%N at once.
@@ -678,7 +738,7 @@ private:
     cudaStream_t s0_ = nullptr, s1_ = nullptr;
     void* send_ = nullptr;
     void* recv_ = nullptr;
-    size_t cap_ = 0, recv_cap_ = 0;
+    size_t cap_ = 0, recv_cap_ = 0, send_cap_ = 0;
     int slots_ = 1;
     cudaEvent_t ev_[4] = {};
     FILE* json_ = nullptr;
@@ -708,13 +768,15 @@ int run_main(Backend& be, int argc, char** argv) {
     Driver<Backend> d(be, opt, rank, world_size);
     const bool sweepish = opt.mode == "sweep" || opt.mode == "latency" || opt.mode == "local";
     const size_t max_bytes = sweepish ? std::max(opt.size, opt.sweep_max) : opt.size;
-    d.setup(max_bytes, opt.mode == "allpairs" ? world_size - 1 : 1);
+    if (opt.mode == "alltoall") d.setup(max_bytes, world_size, world_size);
+    else d.setup(max_bytes, opt.mode == "allpairs" ? world_size - 1 : 1);
 
     if (opt.mode == "ref") d.run_ref_tables(true, true);
     else if (opt.mode == "uni") d.run_ref_tables(true, false);
     else if (opt.mode == "bidir") d.run_ref_tables(false, true);
     else if (opt.mode == "allpairs") d.run_allpairs();
     else if (opt.mode == "ring") d.run_ring();
+    else if (opt.mode == "alltoall") d.run_alltoall();
     else if (opt.mode == "sweep") d.run_sweep(false);
     else if (opt.mode == "latency") d.run_sweep(true);
     else if (opt.mode == "local") d.run_local();

@@ -27,6 +27,7 @@ struct EngineBackend {
     void recv(void* buf, size_t bytes, int peer, cudaStream_t s) { P2PCHECK(p2p_recv(buf, bytes, P2P_INT8, peer, s)); }
     void group_start() { P2PCHECK(p2p_group_start()); }  // p2p_matrix.cc:212
     void group_end() { P2PCHECK(p2p_group_end()); }      // p2p_matrix.cc:227
+    void alltoall(const void* send, void* recv, size_t bytes, cudaStream_t s) { P2PCHECK(p2p_alltoall(send, recv, bytes, P2P_INT8, s)); }
 
     void fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s) {
         P2PCHECK(p2p_pattern_fill(buf, bytes, seed, rank, iter, s));

@@ -57,6 +57,15 @@ def test_allpairs_and_ring_verified(built):
             assert "verify: OK" in out, out
 
 
+@pytest.mark.parametrize("n", RANKS)
+def test_alltoall_verified(built, n):
+    """p2p_alltoall: every block on every rank compared with the pattern of the rank it came from,
+    in each protocol range (eager, push, adaptive)."""
+    for size in ("1000", "600K", "2M", "8M"):
+        out = matrix(n, "--mode", "alltoall", "--size", size, "--iters", "3", "--warmup", "1", "--timing", "dev", "--verify")
+        assert "verify: OK" in out and "VERIFY FAILED" not in out, out
+
+
 def test_sweep_verified(built):
     out = matrix(2, "--mode", "sweep", "--sweep-max", "16M", "--iters", "20", "--verify")
     assert "verify: OK" in out
@@ -125,6 +134,21 @@ for it, size in enumerate([8, 4097, n]):
     assert np.array_equal(got[:size], oracle.expected_recv(size, 42, left, it)), (rank, size)
     assert np.all(got[size:] == 0xA5)
     dist.barrier()
+# all-to-all through the binding, against the oracle's law
+blk = (1 << 20) + 5
+a2a_src, a2a_dst = p2p.DeviceBuffer(blk * world), p2p.DeviceBuffer(blk * world + 64)
+p2p.register(a2a_dst.ptr, a2a_dst.nbytes, gather)
+p2p.register(a2a_src.ptr, a2a_src.nbytes, gather)
+a2a_src.tensor().copy_(torch.from_numpy(oracle.alltoall_send(blk, 7, rank, world)))
+a2a_dst.tensor().fill_(0xA5)
+torch.cuda.synchronize()
+dist.barrier()
+p2p.alltoall(a2a_src.ptr, a2a_dst.ptr, blk, p2p.INT8, s)
+s.synchronize()
+p2p.raise_async_error()
+got = a2a_dst.tensor().cpu().numpy()
+assert np.array_equal(got[: blk * world], oracle.expected_alltoall_recv(blk, 7, rank, world)), rank
+assert np.all(got[blk * world:] == 0xA5)
 torch.cuda.synchronize()
 dist.barrier()
 p2p.finalize()

@@ -274,6 +274,24 @@ def test_full_size_256mib_properties(eng, p2p, oracle):
         dst.free()
 
 
+@pytest.mark.parametrize("block", [0, 8, 4097, 600_001, (5 << 20) + 3])
+def test_alltoall_one_rank(eng, block):
+    """p2p_alltoall with a world of one: its only block is the local one, checked against the
+    oracle's all-to-all law (tests/test_gpu_multi.py runs it across GPUs)."""
+    p2p, torch = eng.p2p, eng.torch
+    p2p.set_option("path", p2p.PATH_AUTO)
+    want_send = eng.oracle.alltoall_send(block, SEED, 0, 1)
+    eng.src.tensor()[:block].copy_(torch.from_numpy(want_send)) if block else None
+    eng.dst.tensor().fill_(0xA5)
+    torch.cuda.synchronize()
+    p2p.alltoall(eng.src.ptr, eng.dst.ptr, block, p2p.INT8, eng.stream)
+    eng.stream.synchronize()
+    p2p.raise_async_error()
+    got = eng.dst.tensor()[: block + 32].cpu().numpy()
+    assert np.array_equal(got[:block], eng.oracle.expected_alltoall_recv(block, SEED, 0, 1))
+    assert np.all(got[block:] == 0xA5)
+
+
 def test_unregistered_receive_buffer_is_refused(eng):
     if not eng.loopback:
         pytest.skip("a matched self send/recv is a local copy and needs no window")
