@@ -409,7 +409,12 @@ int launch_pending() {
             r.proto = PROTO_COPY;
             if (op.is_send) {
                 ++nops_out;
-                if (self_copy_flavour(op.nbytes) == 2) flavour = FLAVOUR_TMA;
+                // the TMA ring is the faster LOCAL copy; with peers in the group the whole launch stays ld/st
+                // (128-thread CTAs and one CTA per SM would starve the peer roles)
+                bool peers_in_group = false;
+                for (size_t j = 0; j < ops.size(); ++j)
+                    if (partner[j] < 0) peers_in_group = true;
+                if (!peers_in_group && self_copy_flavour(op.nbytes) == 2) flavour = FLAVOUR_TMA;
             }
             continue;
         }

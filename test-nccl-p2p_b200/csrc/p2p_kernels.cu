@@ -37,7 +37,8 @@ p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
     pdl_prologue(a.h);
     CopyJob job;
     if (!resolve_role(a.h, a.ops, &slot, job)) return;
-    if ((((uint64_t)job.dst ^ (uint64_t)job.src) & 15) == 0)
+    // the ring stages pushes and local copies; a pull (peer -> local) keeps the register loop
+    if ((((uint64_t)job.dst ^ (uint64_t)job.src) & 15) == 0 && job.op->kind != OP_RECV_ADAPT)
         tma_push(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty);
     else
         copy_bytes(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks);
