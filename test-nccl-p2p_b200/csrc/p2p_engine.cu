@@ -284,6 +284,11 @@ int hostbox_create() {
         return fail(P2P_SYSTEM_ERROR, "mmap of the host mailbox failed: %s", strerror(errno));
     }
     g.hostbox = (HostPost*)m;  // fresh shared memory is zero-filled: no entry is valid
+    static bool registered = false;
+    if (!registered) {  // the reference never tears anything down (p2p_matrix.cc:270-274): do not leak the name
+        atexit([] { if (g.hostbox_name[0]) shm_unlink(g.hostbox_name); });
+        registered = true;
+    }
     return P2P_SUCCESS;
 }
 
