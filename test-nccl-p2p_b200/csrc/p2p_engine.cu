@@ -846,9 +846,10 @@ int p2p_init(int rank, int nranks, int device) {
     g.hostbox = nullptr;
     g.hostbox_name[0] = '\0';
     g.hostbox_bytes = sizeof(HostPost) * (size_t)nranks * nranks * kRing;
-    if (nranks > 1 && rank == 0) {
-        int rc = hostbox_create();
-        if (rc) return rc;
+    if (nranks > 1 && rank == 0 && hostbox_create() != P2P_SUCCESS) {
+        // only the opt-in copy-engine path needs the mailbox; without /dev/shm everything else still works
+        g.hostbox = nullptr;
+        g.hostbox_name[0] = '\0';
     }
     CUDA_TRY(cudaEventCreateWithFlags(&g.ce_fork, cudaEventDisableTiming));
     g.stat_launches = g.stat_ce_copies = 0;
