@@ -102,6 +102,32 @@ int main(int argc, char** argv) {
         free(r2);
     }
 
+    /* tags: MPI_ANY_TAG accepts, a wrong tag is reported; a short receive buffer truncates */
+    if (size > 1) {
+        int v = 41, got = 0;
+        MPI_Status st;
+        if (rank == 0) {
+            REQUIRE(MPI_Send(&v, 1, MPI_INT, 1, 9, MPI_COMM_WORLD) == MPI_SUCCESS);
+            REQUIRE(MPI_Send(&v, 1, MPI_INT, 1, 10, MPI_COMM_WORLD) == MPI_SUCCESS);
+            int two[2] = {1, 2};
+            REQUIRE(MPI_Send(two, 2, MPI_INT, 1, 11, MPI_COMM_WORLD) == MPI_SUCCESS);
+            REQUIRE(MPI_Send(&v, 1, MPI_INT, 1, 12, MPI_COMM_WORLD) == MPI_SUCCESS);
+        } else if (rank == 1) {
+            REQUIRE(MPI_Recv(&got, 1, MPI_INT, 0, MPI_ANY_TAG, MPI_COMM_WORLD, &st) == MPI_SUCCESS);
+            REQUIRE(got == 41 && st.MPI_TAG == 9);
+            REQUIRE(MPI_Recv(&got, 1, MPI_INT, 0, 77, MPI_COMM_WORLD, &st) == MPI_ERR_TAG);
+            REQUIRE(MPI_Recv(&got, 1, MPI_INT, 0, 11, MPI_COMM_WORLD, &st) == MPI_ERR_TRUNCATE);
+            REQUIRE(got == 1);
+            REQUIRE(MPI_Recv(&got, 1, MPI_INT, 0, 12, MPI_COMM_WORLD, &st) == MPI_SUCCESS);  /* the stream is still in step */
+            REQUIRE(got == 41);
+        }
+        /* argument errors */
+        REQUIRE(MPI_Send(&v, 1, MPI_INT, size, 0, MPI_COMM_WORLD) == MPI_ERR_RANK);
+        REQUIRE(MPI_Send(&v, 1, 12345, 0, 0, MPI_COMM_WORLD) == MPI_ERR_TYPE);
+        REQUIRE(MPI_Send(&v, -1, MPI_INT, 0, 0, MPI_COMM_WORLD) == MPI_ERR_ARG);
+        REQUIRE(MPI_Barrier(MPI_COMM_NULL) == MPI_ERR_COMM);
+    }
+
     /* zero-byte message and many barriers */
     if (size > 1) {
         if (rank == 0) REQUIRE(MPI_Send(m, 0, MPI_BYTE, 1, 0, MPI_COMM_WORLD) == MPI_SUCCESS);
