@@ -42,7 +42,7 @@ endif
 export MPI_INC MPI_LIB MPIRUN
 
 ENGINE_SRCS := $(CSRC)/p2p_engine.cu $(CSRC)/p2p_kernels.cu
-ENGINE_HDRS := include/p2p.h $(CSRC)/p2p_internal.h $(CSRC)/p2p_device.cuh $(CSRC)/p2p_tma.cuh
+ENGINE_HDRS := include/p2p.h $(CSRC)/p2p_debug.h $(CSRC)/p2p_internal.h $(CSRC)/p2p_device.cuh $(CSRC)/p2p_tma.cuh
 ENGINE_OBJS := $(BUILD)/p2p_engine.o $(BUILD)/p2p_kernels.o
 
 all: $(LIBDIR)/libb200p2p.so p2p_matrix mpirun-link

@@ -2,6 +2,7 @@
 // turns p2p_send/p2p_recv calls into one fused kernel launch, plan selection, error reporting.
 // C ABI in include/p2p.h; reference call sites it stands in for are cited there.
 #include "p2p.h"
+#include "p2p_debug.h"
 #include "p2p_internal.h"
 
 #include <algorithm>
@@ -156,6 +157,12 @@ struct Engine {
     cudaEvent_t ce_join[P2P_MAX_RANKS] = {};
     cudaEvent_t ce_fork = nullptr;
     long long stat_launches = 0, stat_ce_copies = 0;
+
+    // plan-only mode (p2p_debug.h): groups are resolved exactly as usual but captured instead of launched
+    bool plan_only = false;
+    GroupArgs last_args;
+    uint32_t last_grid = 0, last_block = 0;
+    int last_flavour = 0;
 
     int group_depth = 0;
     std::vector<PendingOp> group_ops;
@@ -641,6 +648,14 @@ int launch_pending() {
     // small eager-only groups run with 128-thread CTAs: less to launch on the latency path
     const uint32_t block = (flavour == FLAVOUR_LDST && only_small && eager_total <= 8192) ? 128 : kLdstThreads;
 
+    if (g.plan_only) {  // CPU tests of the host logic: no device, nothing to launch
+        g.last_args = args;
+        g.last_grid = grid;
+        g.last_block = block;
+        g.last_flavour = flavour;
+        return P2P_SUCCESS;
+    }
+
     // streams: launch on the first op's stream; the others wait for the kernel and it for them
     cudaStream_t launch_stream = ops[0].stream;
     std::vector<cudaStream_t> others;
@@ -936,6 +951,20 @@ int p2p_connect(const void* all_blobs) {
 int p2p_finalize(void) {
     std::lock_guard<std::mutex> lk(g.mu);
     if (!g.inited) return P2P_SUCCESS;
+    if (g.plan_only) {  // nothing was allocated
+        for (int w = 0; w < P2P_MAX_WINDOWS; ++w) g.windows[w] = Window();
+        for (int r = 0; r < P2P_MAX_RANKS; ++r) {
+            g.peer_ctl[r] = nullptr;
+            g.rdv_send_seq[r] = g.rdv_recv_seq[r] = g.ll_send_seq[r] = g.ll_recv_seq[r] = 0;
+        }
+        g.ctl = nullptr;
+        g.arrive = nullptr;
+        g.win_table = nullptr;
+        g.group_ops.clear();
+        g.group_depth = 0;
+        g.plan_only = g.inited = g.connected = false;
+        return P2P_SUCCESS;
+    }
     cudaSetDevice(g.device);
     cudaDeviceSynchronize();
     for (int w = 0; w < P2P_MAX_WINDOWS; ++w) {
@@ -1292,6 +1321,75 @@ int p2p_pattern_check(const void* buf, size_t bytes, uint64_t seed, int rank, ui
 
 int p2p_digest(const void* buf, size_t bytes, p2p_stream_t stream, uint64_t* digest) {
     return run_check(buf, bytes, 0, 0, (cudaStream_t)stream, nullptr, nullptr, digest);
+}
+
+// ---- plan-only mode, for CPU tests of the host logic (declared in csrc/p2p_debug.h, not in p2p.h) ----
+
+int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int ctas_tma) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (g.inited) return fail(P2P_INVALID_USAGE, "engine already initialised");
+    if (nranks < 1 || nranks > P2P_MAX_RANKS || rank < 0 || rank >= nranks) return fail(P2P_INVALID_ARGUMENT, "bad rank/nranks");
+    g.rank = rank;
+    g.nranks = nranks;
+    g.device = 0;
+    g.sm_count = sm_count;
+    g.ctas_ldst = ctas_ldst;
+    g.ctas_tma = ctas_tma;
+    Options& o = g.opt;
+    o = Options();
+    o.path = env_ll("P2P_PATH", o.path);
+    o.nblocks = env_ll("P2P_NBLOCKS", o.nblocks);
+    o.self_nblocks = env_ll("P2P_SELF_NBLOCKS", o.self_nblocks);
+    o.eager_bytes = env_ll("P2P_EAGER_BYTES", o.eager_bytes);
+    o.pull_nblocks = env_ll("P2P_PULL_NBLOCKS", o.pull_nblocks);
+    o.eager_nblocks = env_ll("P2P_EAGER_NBLOCKS", o.eager_nblocks);
+    o.pull_min_bytes = env_ll("P2P_PULL_MIN_BYTES", o.pull_min_bytes);
+    o.pdl = env_ll("P2P_PDL", o.pdl);
+    o.loopback = env_ll("P2P_LOOPBACK", o.loopback);
+    o.bidir_push = env_ll("P2P_BIDIR_PUSH", o.bidir_push);
+    o.tma_min_bytes = env_ll("P2P_TMA_MIN_BYTES", o.tma_min_bytes);
+    o.self_tma_min_bytes = env_ll("P2P_SELF_TMA_MIN_BYTES", o.self_tma_min_bytes);
+    // the same layout arithmetic as p2p_init, over made-up base addresses: rank r's control region "lives" at
+    // P2P_DEBUG_CTL_BASE + r * P2P_DEBUG_CTL_STRIDE, so tests can tell whose memory a flag address points into
+    g.ll_slot_bytes = ((size_t)std::max<long long>(o.eager_bytes, 8) * 2 + 255) & ~(size_t)255;
+    g.ll_off = (sizeof(PeerCtl) * (size_t)nranks + 4095) & ~(size_t)4095;
+    g.ctl_bytes = g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes;
+    for (int r = 0; r < nranks; ++r) g.peer_ctl[r] = (uint8_t*)(0x100000000000ull + (uint64_t)r * 0x1000000000ull);
+    g.ctl = g.peer_ctl[rank];
+    g.arrive = (uint32_t*)0x200000000000ull;
+    g.win_table = (uint64_t*)0x300000000000ull;
+    g.hostbox = nullptr;
+    g.async_err_dev = nullptr;
+    g.plan_only = g.inited = g.connected = true;
+    return P2P_SUCCESS;
+}
+
+// Pretend `base .. base+bytes` is a registered window of this rank (every rank contributing).
+int p2p_debug_plan_window(uint64_t base, size_t bytes) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.plan_only) return fail(P2P_INVALID_USAGE, "not in plan-only mode");
+    for (int w = 0; w < P2P_MAX_WINDOWS; ++w)
+        if (!g.windows[w].used) {
+            Window W;
+            W.used = true;
+            W.base = (uint8_t*)base;
+            W.bytes = bytes;
+            for (int r = 0; r < g.nranks; ++r) W.peer_base[r] = (uint8_t*)(base + ((uint64_t)(r + 1) << 44));
+            g.windows[w] = W;
+            return w;
+        }
+    return -1;
+}
+
+// The last group as it would have been launched: raw GroupArgs (layout in p2p_device.cuh) + launch shape.
+int p2p_debug_plan_last(void* args_out, size_t args_bytes, uint32_t* grid, uint32_t* block, int* flavour) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.plan_only) return fail(P2P_INVALID_USAGE, "not in plan-only mode");
+    if (args_out) memcpy(args_out, &g.last_args, std::min(args_bytes, sizeof g.last_args));
+    if (grid) *grid = g.last_grid;
+    if (block) *block = g.last_block;
+    if (flavour) *flavour = g.last_flavour;
+    return (int)sizeof g.last_args;
 }
 
 }  // extern "C"
