@@ -74,7 +74,11 @@ mpirun-link: $(MPI_DEP)
 oracle: $(MPI_DEP) $(BUILD)/libb200p2p.a
 	$(MAKE) -C oracle
 
-tests: $(BUILD)/minimpi_selftest $(BUILD)/driver_unit
+tests: $(BUILD)/minimpi_selftest $(BUILD)/driver_unit $(BUILD)/mpi_glue_nogpu
+
+$(BUILD)/mpi_glue_nogpu: tests/csrc/mpi_glue_nogpu.cc include/p2p.h include/p2p_mpi.h $(BUILD)/libb200p2p.a $(MPI_DEP)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(ARCH) -std=c++17 -O1 -Iinclude $(MPI_INC) $< $(BUILD)/libb200p2p.a $(MPI_LIB) -o $@
 
 $(BUILD)/driver_unit: tests/csrc/driver_unit.cc $(PKG)/host/matrix_driver.hpp $(MPI_DEP)
 	@mkdir -p $(BUILD)

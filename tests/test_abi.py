@@ -119,3 +119,15 @@ def test_product_does_not_link_the_oracle(p2p):
             if f.endswith((".cu", ".cuh", ".cc", ".hpp", ".h", ".py")):
                 text = open(os.path.join(root, f)).read()
                 assert '#include "pattern.h"' not in text and "import pattern" not in text, f
+
+
+@pytest.mark.skipif(gpu_count() > 0, reason="this box has a GPU")
+@pytest.mark.parametrize("n", [1, 2, 4])
+def test_mpi_glue_fails_on_every_rank_without_hanging(built, n):
+    """include/p2p_mpi.h: when the engine cannot start, all ranks learn it and leave the collectives together."""
+    exe = os.path.join(ROOT, "build", "mpi_glue_nogpu")
+    if not os.path.exists(exe):
+        run(["make", "tests"])
+    out = run([MPIRUN, "-n", str(n), exe], timeout=60).stdout
+    lines = [l for l in out.splitlines() if l.startswith("rank ")]
+    assert len(lines) == n and all("init=1 (unhandled cuda error)" in l for l in lines), out
