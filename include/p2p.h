@@ -31,6 +31,12 @@
  * agree, calls return after enqueue and complete in stream order, and a send and a recv
  * that must make progress together (bidirectional exchange, self-send) belong in one
  * p2p_group_start()/p2p_group_end() pair.
+ *
+ * Limits.  At most P2P_MAX_RANKS ranks, P2P_MAX_WINDOWS windows per rank, P2P_MAX_GROUP_OPS
+ * operations per group, messages below 512 GiB, and at most 64 rendezvous-sized (4 eager-sized)
+ * messages in flight per ordered pair of ranks — more than any one stream can have outstanding,
+ * since each receive holds its stream until its payload has landed.  One host thread at a time.
+ * Calls are not capturable into CUDA graphs (sequence numbers are assigned when a call is made).
  */
 #ifndef B200_P2P_H
 #define B200_P2P_H
@@ -158,7 +164,11 @@ P2P_API int p2p_get_async_error(int* result);
  *      "tma_chunk", "tma_stages", "tma_min_bytes", "pdl" (programmatic dependent launch),
  *      "loopback" (send-to-self goes through the wire protocol; for tests).  Environment:
  *      P2P_PATH, P2P_NBLOCKS, P2P_PULL_NBLOCKS, P2P_SELF_NBLOCKS, P2P_EAGER_BYTES, P2P_PULL_MIN_BYTES,
- *      P2P_TIMEOUT_MS, P2P_TMA_CHUNK, P2P_TMA_STAGES, P2P_TMA_MIN_BYTES, P2P_PDL, P2P_LOOPBACK. ---- */
+ *      P2P_TIMEOUT_MS, P2P_TMA_CHUNK, P2P_TMA_STAGES, P2P_TMA_MIN_BYTES, P2P_PDL, P2P_LOOPBACK,
+ *      P2P_BIDIR_PUSH, P2P_SELF_TMA_MIN_BYTES, and the experimental copy-engine path
+ *      P2P_CE_MIN_BYTES / P2P_CE_WAIT_US (off by default: measured slower than the pull kernel).
+ *      p2p_get_option also answers "sm_count", "ctas_per_sm_ldst", "ctas_per_sm_tma",
+ *      "stat_launches" (kernels launched so far) and "stat_ce_copies". ---- */
 P2P_API int p2p_set_option(const char* name, long long value);
 P2P_API int p2p_get_option(const char* name, long long* value);
 /* What the selector would do for a message of `bytes` to `peer`: writes the path id
