@@ -85,7 +85,7 @@ def main():
             o = args.ops[i]
             rec["ops"].append({
                 "kind": KINDS[o.kind], "local": o.local, "nbytes": o.nbytes, "seq": o.seq, "peer": o.peer,
-                "first_block": o.first_block, "nblocks": o.nblocks, "word": o.word, "word2": o.word2, "aux": o.aux,
+                "first_block": o.first_block, "nblocks": o.nblocks, "word": o.word, "word2": o.word2, "aux": o.aux, "arrive": o.arrive,
                 "wait_owner": owner(o.f_wait), "signal_owner": owner(o.f_signal),
                 "wait2_owner": owner(o.f_wait2), "signal2_owner": owner(o.f_signal2),
                 "f_wait": o.f_wait, "f_signal": o.f_signal, "f_wait2": o.f_wait2, "f_signal2": o.f_signal2,

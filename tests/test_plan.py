@@ -205,3 +205,16 @@ def test_group_limits():
     too_many = [["send", SEND_WIN, 8, 1]] * 33
     (g,) = plan(0, 2, [too_many])
     assert g["rc"] == 5 and "at most 32" in g["error"]
+
+
+def test_plan_snapshot():
+    """Every field of every kernel argument, for a fixed set of scenarios, against tests/golden/plan_snapshot.json
+    (tests/make_plan_snapshot.py).  A difference is either a regression or an intended change of the planner
+    that has to be re-measured on GPUs and re-recorded."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import make_plan_snapshot
+    golden = json.load(open(os.path.join(ROOT, "tests", "golden", "plan_snapshot.json")))
+    now = make_plan_snapshot.snapshot()
+    assert sorted(now) == sorted(golden)
+    for name in golden:
+        assert now[name] == golden[name], f"planner output changed for scenario {name}"
