@@ -379,54 +379,77 @@ inline uint32_t* arrive_pull(int p, uint64_t seq) { return g.arrive + (size_t)(g
 inline uint32_t* arrive_ll(int p, uint64_t seq) { return g.arrive + (size_t)2 * g.nranks * kRing + (size_t)p * kLLSlots + seq % kLLSlots; }
 
 // ---- group launch --------------------------------------------------------------------
+//
+// launch_pending() turns the operations collected since p2p_group_start (or a single ungrouped call) into one
+// kernel launch.  Steps, each a function below:
+//   match_self_pairs   a send to oneself and a receive from oneself become one local copy
+//   resolve_protocols  protocol per message, window lookup, who moves the bytes; everything that can be refused
+//   assign_sequence    sequence numbers in program order; large receives tell the sender's host where they go
+//   choose_copy_engine the opt-in DMA path for a lone large send
+//   size_roles         CTAs per role, scaled so that the whole launch is co-resident
+//   build_args         the kernel's argument block: roles, flags, block ranges
+//   submit             stream dependencies, the launch, copy-engine chains
 
-int launch_pending() {
-    std::vector<PendingOp> ops;
-    ops.swap(g.group_ops);
-    if (ops.empty()) return P2P_SUCCESS;
-    const int me = g.rank;
+struct Resolved {
+    Proto proto;
+    uint32_t win;
+    uint64_t off;
+    bool registered;
+    bool pull_send;   // large send that lets the receiver pull
+    int nblocks;
+    uint64_t seq;
+    bool ce;          // large send handed to the copy engine
+    uint64_t ce_word;
+};
 
-    // a send to oneself and a receive from oneself in the same group are one local copy
-    std::vector<int> partner(ops.size(), -1);
-    if (!g.opt.loopback) {
-        std::vector<size_t> self_sends, self_recvs;
-        for (size_t i = 0; i < ops.size(); ++i)
-            if (ops[i].peer == me) (ops[i].is_send ? self_sends : self_recvs).push_back(i);
-        for (size_t k = 0; k < std::min(self_sends.size(), self_recvs.size()); ++k) {
-            const size_t si = self_sends[k], ri = self_recvs[k];
-            if (ops[si].nbytes != ops[ri].nbytes)
-                return fail(P2P_INVALID_ARGUMENT, "send to self of %zu bytes is matched by a receive of %zu bytes", ops[si].nbytes,
-                            ops[ri].nbytes);
-            partner[si] = (int)ri;
-            partner[ri] = (int)si;
-        }
-    }
-
+struct GroupShape {
+    int flavour = FLAVOUR_LDST;
     int n_large_sends = 0, n_large_recvs = 0;
+    uint32_t n_ctrl = 0;
+    size_t eager_total = 0;
+    bool only_small = true;
+    bool any_ce = false;
+};
+
+int match_self_pairs(const std::vector<PendingOp>& ops, std::vector<int>& partner) {
+    partner.assign(ops.size(), -1);
+    if (g.opt.loopback) return P2P_SUCCESS;
+    std::vector<size_t> self_sends, self_recvs;
+    for (size_t i = 0; i < ops.size(); ++i)
+        if (ops[i].peer == g.rank) (ops[i].is_send ? self_sends : self_recvs).push_back(i);
+    for (size_t k = 0; k < std::min(self_sends.size(), self_recvs.size()); ++k) {
+        const size_t si = self_sends[k], ri = self_recvs[k];
+        if (ops[si].nbytes != ops[ri].nbytes)
+            return fail(P2P_INVALID_ARGUMENT, "send to self of %zu bytes is matched by a receive of %zu bytes", ops[si].nbytes,
+                        ops[ri].nbytes);
+        partner[si] = (int)ri;
+        partner[ri] = (int)si;
+    }
+    return P2P_SUCCESS;
+}
+
+// Nothing here changes engine state: a group that is refused leaves every sequence number where it was.
+int resolve_protocols(const std::vector<PendingOp>& ops, const std::vector<int>& partner, std::vector<Resolved>& res,
+                      GroupShape& shape) {
     for (size_t i = 0; i < ops.size(); ++i)
         if (partner[i] < 0 && is_large(ops[i].nbytes) && (long long)ops[i].nbytes > g.opt.eager_bytes)
-            (ops[i].is_send ? n_large_sends : n_large_recvs)++;
+            (ops[i].is_send ? shape.n_large_sends : shape.n_large_recvs)++;
+    bool peers_in_group = false;
+    for (size_t j = 0; j < ops.size(); ++j)
+        if (partner[j] < 0) peers_in_group = true;
 
-    // validate everything before any sequence number moves
-    struct Resolved { Proto proto; uint32_t win; uint64_t off; bool registered; bool pull_send; int nblocks;
-                      uint64_t seq; bool ce; uint64_t ce_word; };
-    std::vector<Resolved> res(ops.size());
-    int flavour = FLAVOUR_LDST;
+    res.assign(ops.size(), Resolved{});
     size_t nops_out = 0;
     for (size_t i = 0; i < ops.size(); ++i) {
         const PendingOp& op = ops[i];
         Resolved& r = res[i];
-        r = Resolved{};
         if (partner[i] >= 0) {
             r.proto = PROTO_COPY;
             if (op.is_send) {
                 ++nops_out;
                 // the TMA ring is the faster LOCAL copy; with peers in the group the whole launch stays ld/st
                 // (128-thread CTAs and one CTA per SM would starve the peer roles)
-                bool peers_in_group = false;
-                for (size_t j = 0; j < ops.size(); ++j)
-                    if (partner[j] < 0) peers_in_group = true;
-                if (!peers_in_group && self_copy_flavour(op.nbytes) == 2) flavour = FLAVOUR_TMA;
+                if (!peers_in_group && self_copy_flavour(op.nbytes) == 2) shape.flavour = FLAVOUR_TMA;
             }
             continue;
         }
@@ -448,16 +471,19 @@ int launch_pending() {
             bool also_receiving = false;
             for (size_t j = 0; j < ops.size(); ++j)
                 if (!ops[j].is_send && ops[j].peer == op.peer && partner[j] < 0 && is_large(ops[j].nbytes)) also_receiving = true;
-            const bool pairwise = also_receiving && n_large_sends == 1 && g.opt.bidir_push;
+            const bool pairwise = also_receiving && shape.n_large_sends == 1 && g.opt.bidir_push;
             r.pull_send = r.registered && !pairwise && g.opt.path != 2 && g.opt.path != 1;
         }
-        if (op.is_send && !(r.proto == PROTO_LARGE && r.pull_send) && push_flavour(op.nbytes) == 2) flavour = FLAVOUR_TMA;
+        if (op.is_send && !(r.proto == PROTO_LARGE && r.pull_send) && push_flavour(op.nbytes) == 2) shape.flavour = FLAVOUR_TMA;
     }
     if (nops_out > (size_t)kMaxGroupOps)
         return fail(P2P_INVALID_USAGE, "a group holds at most %d operations (got %zu)", kMaxGroupOps, nops_out);
+    return P2P_SUCCESS;
+}
 
-    // Sequence numbers in PROGRAM order (the k-th send to a peer pairs with its k-th receive, whatever protocol
-    // each message ends up using); nothing below this point can fail for a reason the peer would not share.
+// Sequence numbers in PROGRAM order (the k-th send to a peer pairs with its k-th receive, whatever protocol each
+// message ends up using).  From here on nothing may fail for a reason the peer would not share.
+void assign_sequence(const std::vector<PendingOp>& ops, std::vector<Resolved>& res) {
     for (size_t i = 0; i < ops.size(); ++i) {
         Resolved& r = res[i];
         if (r.proto == PROTO_COPY) continue;
@@ -465,18 +491,20 @@ int launch_pending() {
         if (r.proto == PROTO_EAGER) r.seq = ops[i].is_send ? ++g.ll_send_seq[p] : ++g.ll_recv_seq[p];
         else r.seq = ops[i].is_send ? ++g.rdv_send_seq[p] : ++g.rdv_recv_seq[p];
         // a large receive also tells the sender's HOST where it goes (copy-engine path)
-        if (!ops[i].is_send && r.proto == PROTO_LARGE && p != me)
+        if (!ops[i].is_send && r.proto == PROTO_LARGE && p != g.rank)
             hostbox_publish(p, r.seq, r.registered ? make_post_word(r.seq, r.win, r.off) : 0);
     }
-    // Copy engine (opt-in) for a send that is alone in its group and whose destination the host already knows.
-    // Alone, because the chain runs beside the group's kernel on another stream and a receive in that kernel
-    // may depend on it: two launches that must overlap are not something a GPU promises.  Never waits longer
-    // than ce_wait_us for the receiver's host; otherwise the SM path is used as if the option were off.
-    bool any_ce = false;
+}
+
+// Copy engine (opt-in) for a send that is alone in its group and whose destination the host already knows.
+// Alone, because the chain runs beside the group's kernel on another stream and a receive in that kernel may
+// depend on it: two launches that must overlap are not something a GPU promises.  Never waits longer than
+// ce_wait_us for the receiver's host; otherwise the SM path is used as if the option were off.
+void choose_copy_engine(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, GroupShape& shape) {
     for (size_t i = 0; i < ops.size(); ++i) {
         Resolved& r = res[i];
         const PendingOp& op = ops[i];
-        if (!(op.is_send && r.proto == PROTO_LARGE && op.peer != me)) continue;
+        if (!(op.is_send && r.proto == PROTO_LARGE && op.peer != g.rank)) continue;
         if (g.opt.ce_min_bytes < 0 || (long long)op.nbytes < g.opt.ce_min_bytes || ops.size() != 1) continue;
         if (g.opt.path != 0 && g.opt.path != 3) continue;
         uint64_t word = 0;
@@ -486,52 +514,50 @@ int launch_pending() {
         r.ce = true;
         r.ce_word = word;
         r.pull_send = false;
-        any_ce = true;
+        shape.any_ce = true;
     }
+}
 
-    // CTA counts
-    const int per_sm = flavour == FLAVOUR_TMA ? g.ctas_tma : g.ctas_ldst;
+// CTAs per role.  Everything must be co-resident: roles wait for peers, and a CTA that cannot get an SM could
+// keep a peer waiting for ever.  Eager roles may take at most half of the machine, movers share what is left.
+void size_roles(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, GroupShape& shape) {
+    const int per_sm = shape.flavour == FLAVOUR_TMA ? g.ctas_tma : g.ctas_ldst;
     long long budget = (long long)g.sm_count * per_sm;
     long long fixed = 0, want = 0;
-    uint32_t n_ctrl = 0;
-    size_t eager_total = 0;
-    bool only_small = true;
     for (size_t i = 0; i < ops.size(); ++i) {
         const PendingOp& op = ops[i];
         Resolved& r = res[i];
-        const bool self = op.peer == me;
+        const bool self = op.peer == g.rank;
         switch (r.proto) {
             case PROTO_COPY:
-                r.nblocks = op.is_send ? mover_ctas(op.nbytes, flavour, true, false) : 0;
+                r.nblocks = op.is_send ? mover_ctas(op.nbytes, shape.flavour, true, false) : 0;
                 want += r.nblocks;
-                if (op.nbytes > 4096) only_small = false;
+                if (op.nbytes > 4096) shape.only_small = false;
                 break;
             case PROTO_EAGER:
                 r.nblocks = eager_ctas(op.nbytes);
                 fixed += r.nblocks;
-                eager_total += op.nbytes;
+                shape.eager_total += op.nbytes;
                 break;
             case PROTO_PUSH:
-                only_small = false;
-                if (op.is_send) { r.nblocks = mover_ctas(op.nbytes, flavour, self, false); want += r.nblocks; }
-                else ++n_ctrl;
+                shape.only_small = false;
+                if (op.is_send) { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false); want += r.nblocks; }
+                else ++shape.n_ctrl;
                 break;
             case PROTO_LARGE:
-                only_small = false;
+                shape.only_small = false;
                 if (op.is_send) {
                     if (r.ce) break;  // moved by the copy engine, outside the kernel
-                    if (r.pull_send) ++n_ctrl;
-                    else { r.nblocks = mover_ctas(op.nbytes, flavour, self, false, n_large_sends); want += r.nblocks; }
+                    if (r.pull_send) ++shape.n_ctrl;
+                    else { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false, shape.n_large_sends); want += r.nblocks; }
                 } else {
-                    r.nblocks = mover_ctas(op.nbytes, FLAVOUR_LDST, self, true, n_large_recvs);
+                    r.nblocks = mover_ctas(op.nbytes, FLAVOUR_LDST, self, true, shape.n_large_recvs);
                     want += r.nblocks;
                 }
                 break;
         }
     }
-    // Everything must be co-resident: roles wait for peers, and a CTA that cannot get an SM could keep a peer waiting
-    // for ever.  Eager roles may take at most half of the machine, movers share what is left.
-    budget -= (n_ctrl ? 1 : 0);
+    budget -= (shape.n_ctrl ? 1 : 0);
     if (fixed > budget / 2) {
         const long long room = std::max<long long>(budget / 2, 1);
         long long now = 0;
@@ -548,20 +574,74 @@ int launch_pending() {
         for (size_t i = 0; i < ops.size(); ++i)
             if (res[i].nblocks > 0 && res[i].proto != PROTO_EAGER)
                 res[i].nblocks = (int)std::max<long long>(1, res[i].nblocks * budget / want);
+}
 
-    GroupArgs args;
+// Fills one role's descriptor: which flags it polls and writes, in whose control region.
+void describe_role(const PendingOp& op, const Resolved& r, const PendingOp* copy_partner, OpDesc& d) {
+    const int me = g.rank, p = op.peer;
+    uint8_t* my = g.ctl;
+    uint8_t* theirs = g.peer_ctl[p];
+    const uint64_t seq = r.seq;
+    d.local = (uint64_t)op.buf;
+    d.nbytes = op.nbytes;
+    d.peer = (uint32_t)p;
+    d.nblocks = (uint32_t)r.nblocks;
+    d.seq = seq;
+    if (r.proto == PROTO_COPY) {
+        d.kind = OP_COPY;
+        d.aux = (uint64_t)copy_partner->buf;
+    } else if (r.proto == PROTO_EAGER && !op.is_send) {
+        d.kind = OP_RECV_LL;
+        d.aux = (uint64_t)ll_slot(my, p, seq);
+        d.f_signal = (uint64_t)&peer_section(theirs, me)->ll_ack[seq % kLLSlots];
+        d.arrive = (uint64_t)arrive_ll(p, seq);
+    } else if (r.proto == PROTO_EAGER) {
+        d.kind = OP_SEND_LL;
+        d.aux = (uint64_t)ll_slot(theirs, me, seq);
+        d.f_wait = (uint64_t)&peer_section(my, p)->ll_ack[seq % kLLSlots];
+    } else if (!op.is_send) {
+        // what a pushing sender needs from me
+        d.word = r.registered ? make_post_word(seq, r.win, r.off) : 0;
+        d.f_signal = (uint64_t)&peer_section(theirs, me)->post[seq % kRing];
+        d.f_wait = (uint64_t)&peer_section(my, p)->done[seq % kRing];
+        if (r.proto == PROTO_PUSH) {
+            d.kind = OP_POST;
+        } else {
+            d.kind = OP_RECV_ADAPT;
+            d.f_wait2 = (uint64_t)&peer_section(my, p)->pull_post[seq % kRing];
+            d.f_signal2 = (uint64_t)&peer_section(theirs, me)->pull_done[seq % kRing];
+            d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
+            d.arrive = (uint64_t)arrive_pull(p, seq);
+        }
+    } else if (r.proto == PROTO_LARGE && r.pull_send) {
+        d.kind = OP_POST;  // publish where my payload lies, wait until it has been read
+        d.word = make_post_word(seq, r.win, r.off);
+        d.f_signal = (uint64_t)&peer_section(theirs, me)->pull_post[seq % kRing];
+        d.f_wait = (uint64_t)&peer_section(my, p)->pull_done[seq % kRing];
+    } else {
+        d.kind = OP_PUSH;
+        d.f_wait = (uint64_t)&peer_section(my, p)->post[seq % kRing];
+        d.f_signal = (uint64_t)&peer_section(theirs, me)->done[seq % kRing];
+        d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
+        d.arrive = (uint64_t)arrive_push(p, seq);
+        if (r.proto == PROTO_LARGE) {  // the receiver is waiting to be told
+            d.f_signal2 = (uint64_t)&peer_section(theirs, me)->pull_post[seq % kRing];
+            d.word2 = make_post_word(seq, kWinPushPlease, 0);
+        }
+    }
+}
+
+// Order of CTAs: control CTA, eager sends (they wait for nothing that runs here), eager receives, large
+// receives (they start by waiting), then everything that pushes or copies.  Returns the grid size.
+uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolved>& res, const std::vector<int>& partner,
+                    const GroupShape& shape, GroupArgs& args) {
     memset(&args, 0, sizeof args);
     args.h.tma_chunk = (uint32_t)g.opt.tma_chunk;
     args.h.tma_stages = (uint32_t)g.opt.tma_stages;
     args.h.timeout_ns = (uint64_t)g.opt.timeout_ms * 1000000ull;
     args.h.async_err = g.async_err_dev;
-    args.h.pdl = 0;  // decided below, once the roles of the group are known
-    args.h.n_ctrl = n_ctrl;
-
-    uint32_t next_block = n_ctrl ? 1 : 0;
-    uint8_t* my = g.ctl;
-    // order of CTAs: control CTA, eager sends (they wait for nothing that runs here), eager receives,
-    // large receives (they start by waiting), then everything that pushes or copies
+    args.h.n_ctrl = shape.n_ctrl;
+    uint32_t next_block = shape.n_ctrl ? 1 : 0;
     for (int pass = 0; pass < 5; ++pass) {
         for (size_t i = 0; i < ops.size(); ++i) {
             const PendingOp& op = ops[i];
@@ -573,90 +653,48 @@ int launch_pending() {
             else cls = op.is_send ? (r.ce ? -1 : r.pull_send ? 0 : 4) : 3;
             if (cls != pass) continue;
             OpDesc& d = args.ops[args.h.nops++];
-            const int p = op.peer;
-            uint8_t* theirs = g.peer_ctl[p];
-            d.local = (uint64_t)op.buf;
-            d.nbytes = op.nbytes;
-            d.peer = (uint32_t)p;
-            d.nblocks = (uint32_t)r.nblocks;
-            if (r.proto == PROTO_COPY) {
-                d.kind = OP_COPY;
-                d.aux = (uint64_t)ops[(size_t)partner[i]].buf;
-            } else if (r.proto == PROTO_EAGER && !op.is_send) {
-                const uint64_t seq = r.seq;
-                d.kind = OP_RECV_LL;
-                d.seq = seq;
-                d.aux = (uint64_t)ll_slot(my, p, seq);
-                d.f_signal = (uint64_t)&peer_section(theirs, me)->ll_ack[seq % kLLSlots];
-                d.arrive = (uint64_t)arrive_ll(p, seq);
-            } else if (r.proto == PROTO_EAGER) {
-                const uint64_t seq = r.seq;
-                d.kind = OP_SEND_LL;
-                d.seq = seq;
-                d.aux = (uint64_t)ll_slot(theirs, me, seq);
-                d.f_wait = (uint64_t)&peer_section(my, p)->ll_ack[seq % kLLSlots];
-            } else if (!op.is_send) {
-                const uint64_t seq = r.seq;
-                d.seq = seq;
-                // what a pushing sender needs from me
-                d.word = r.registered ? make_post_word(seq, r.win, r.off) : 0;
-                d.f_signal = (uint64_t)&peer_section(theirs, me)->post[seq % kRing];
-                d.f_wait = (uint64_t)&peer_section(my, p)->done[seq % kRing];
-                if (r.proto == PROTO_PUSH) {
-                    d.kind = OP_POST;
-                } else {
-                    d.kind = OP_RECV_ADAPT;
-                    d.f_wait2 = (uint64_t)&peer_section(my, p)->pull_post[seq % kRing];
-                    d.f_signal2 = (uint64_t)&peer_section(theirs, me)->pull_done[seq % kRing];
-                    d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
-                    d.arrive = (uint64_t)arrive_pull(p, seq);
-                }
-            } else {
-                const uint64_t seq = r.seq;
-                d.seq = seq;
-                if (r.proto == PROTO_LARGE && r.pull_send) {
-                    d.kind = OP_POST;  // publish where my payload lies, wait until it has been read
-                    d.word = make_post_word(seq, r.win, r.off);
-                    d.f_signal = (uint64_t)&peer_section(theirs, me)->pull_post[seq % kRing];
-                    d.f_wait = (uint64_t)&peer_section(my, p)->pull_done[seq % kRing];
-                } else {
-                    d.kind = OP_PUSH;
-                    d.f_wait = (uint64_t)&peer_section(my, p)->post[seq % kRing];
-                    d.f_signal = (uint64_t)&peer_section(theirs, me)->done[seq % kRing];
-                    d.aux = (uint64_t)(g.win_table + (size_t)p * P2P_MAX_WINDOWS);
-                    d.arrive = (uint64_t)arrive_push(p, seq);
-                    if (r.proto == PROTO_LARGE) {  // the receiver is waiting to be told
-                        d.f_signal2 = (uint64_t)&peer_section(theirs, me)->pull_post[seq % kRing];
-                        d.word2 = make_post_word(seq, kWinPushPlease, 0);
-                    }
-                }
-            }
+            describe_role(op, r, r.proto == PROTO_COPY ? &ops[(size_t)partner[i]] : nullptr, d);
             if (d.kind != OP_POST) {
                 d.first_block = next_block;
                 next_block += d.nblocks;
             }
         }
     }
-    const uint32_t grid = next_block;
-    if (grid == 0 && !any_ce) return P2P_SUCCESS;
     bool light = true;  // no rendezvous role in the group
     for (uint32_t i = 0; i < args.h.nops; ++i) {
         const uint32_t k = args.ops[i].kind;
         if (k == OP_POST || k == OP_PUSH || k == OP_RECV_ADAPT) light = false;
     }
-    args.h.pdl = (g.opt.pdl == 2 || (g.opt.pdl == 1 && light && !any_ce)) ? 1 : 0;
-    // small eager-only groups run with 128-thread CTAs: less to launch on the latency path
-    const uint32_t block = (flavour == FLAVOUR_LDST && only_small && eager_total <= 8192) ? 128 : kLdstThreads;
+    args.h.pdl = (g.opt.pdl == 2 || (g.opt.pdl == 1 && light && !shape.any_ce)) ? 1 : 0;
+    return next_block;
+}
 
-    if (g.plan_only) {  // CPU tests of the host logic: no device, nothing to launch
-        g.last_args = args;
-        g.last_grid = grid;
-        g.last_block = block;
-        g.last_flavour = flavour;
-        return P2P_SUCCESS;
+// One copy-engine chain: ce_wait (announce the push, wait for the receiver's post) -> DMA -> ce_signal.
+int submit_copy_engine_chain(const PendingOp& op, const Resolved& r, const GroupHdr& hdr, cudaStream_t launch_stream) {
+    const int me = g.rank, p = op.peer;
+    const uint64_t seq = r.seq, word = r.ce_word;
+    if (!g.ce_stream[p]) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&g.ce_stream[p], cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&g.ce_join[p], cudaEventDisableTiming));
     }
+    uint8_t* theirs = g.peer_ctl[p];
+    uint8_t* dst = g.windows[(word >> 40) & 0xffu].peer_base[p] + (word & kPostOffMask);
+    cudaStream_t cs = g.ce_stream[p];
+    CUDA_TRY(cudaStreamWaitEvent(cs, g.ce_fork, 0));
+    CUDA_TRY(launch_ce_wait(&peer_section(theirs, me)->pull_post[seq % kRing], make_post_word(seq, kWinPushPlease, 0),
+                            &peer_section(g.ctl, p)->post[seq % kRing], seq, word, hdr, cs));
+    CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
+    CUDA_TRY(launch_ce_signal(&peer_section(theirs, me)->done[seq % kRing], seq, cs));
+    CUDA_TRY(cudaEventRecord(g.ce_join[p], cs));
+    CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ce_join[p], 0));
+    g.stat_launches += 2;
+    g.stat_ce_copies++;
+    return P2P_SUCCESS;
+}
 
-    // streams: launch on the first op's stream; the others wait for the kernel and it for them
+// Streams: launch on the first op's stream; the others wait for the kernel and it for them.
+int submit(const std::vector<PendingOp>& ops, const std::vector<Resolved>& res, const GroupShape& shape, const GroupArgs& args,
+           uint32_t grid, uint32_t block) {
     cudaStream_t launch_stream = ops[0].stream;
     std::vector<cudaStream_t> others;
     for (const PendingOp& op : ops)
@@ -673,41 +711,54 @@ int launch_pending() {
     }
     // copy-engine chains fork off BEFORE the kernel: the kernel may hold a receive that only completes once
     // the peer's chain has run, and the peer's chain may need ours
-    if (any_ce) CUDA_TRY(cudaEventRecord(g.ce_fork, launch_stream));
+    if (shape.any_ce) CUDA_TRY(cudaEventRecord(g.ce_fork, launch_stream));
     if (grid > 0) {
-        const int dyn_smem = flavour == FLAVOUR_TMA ? (int)(g.opt.tma_chunk * g.opt.tma_stages) : 0;
-        CUDA_TRY(launch_group(flavour, args, grid, block, dyn_smem, launch_stream));
+        const int dyn_smem = shape.flavour == FLAVOUR_TMA ? (int)(g.opt.tma_chunk * g.opt.tma_stages) : 0;
+        CUDA_TRY(launch_group(shape.flavour, args, grid, block, dyn_smem, launch_stream));
         g.stat_launches++;
     }
-    if (any_ce) {
-        for (size_t i = 0; i < ops.size(); ++i) {
-            if (!res[i].ce) continue;
-            const PendingOp& op = ops[i];
-            const int p = op.peer;
-            const uint64_t seq = res[i].seq, word = res[i].ce_word;
-            if (!g.ce_stream[p]) {
-                CUDA_TRY(cudaStreamCreateWithFlags(&g.ce_stream[p], cudaStreamNonBlocking));
-                CUDA_TRY(cudaEventCreateWithFlags(&g.ce_join[p], cudaEventDisableTiming));
+    if (shape.any_ce)
+        for (size_t i = 0; i < ops.size(); ++i)
+            if (res[i].ce) {
+                int rc = submit_copy_engine_chain(ops[i], res[i], args.h, launch_stream);
+                if (rc) return rc;
             }
-            uint8_t* theirs = g.peer_ctl[p];
-            uint8_t* dst = g.windows[(word >> 40) & 0xffu].peer_base[p] + (word & kPostOffMask);
-            cudaStream_t cs = g.ce_stream[p];
-            CUDA_TRY(cudaStreamWaitEvent(cs, g.ce_fork, 0));
-            CUDA_TRY(launch_ce_wait(&peer_section(theirs, me)->pull_post[seq % kRing], make_post_word(seq, kWinPushPlease, 0),
-                                    &peer_section(my, p)->post[seq % kRing], seq, word, args.h, cs));
-            CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
-            CUDA_TRY(launch_ce_signal(&peer_section(theirs, me)->done[seq % kRing], seq, cs));
-            CUDA_TRY(cudaEventRecord(g.ce_join[p], cs));
-            CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ce_join[p], 0));
-            g.stat_launches += 2;
-            g.stat_ce_copies++;
-        }
-    }
     if (!others.empty()) {
         CUDA_TRY(cudaEventRecord(g.ev_done, launch_stream));
         for (cudaStream_t s : others) CUDA_TRY(cudaStreamWaitEvent(s, g.ev_done, 0));
     }
     return P2P_SUCCESS;
+}
+
+int launch_pending() {
+    std::vector<PendingOp> ops;
+    ops.swap(g.group_ops);
+    if (ops.empty()) return P2P_SUCCESS;
+
+    std::vector<int> partner;
+    std::vector<Resolved> res;
+    GroupShape shape;
+    int rc = match_self_pairs(ops, partner);
+    if (rc == P2P_SUCCESS) rc = resolve_protocols(ops, partner, res, shape);
+    if (rc != P2P_SUCCESS) return rc;
+    assign_sequence(ops, res);
+    choose_copy_engine(ops, res, shape);
+    size_roles(ops, res, shape);
+
+    GroupArgs args;
+    const uint32_t grid = build_args(ops, res, partner, shape, args);
+    if (grid == 0 && !shape.any_ce) return P2P_SUCCESS;
+    // small eager-only groups run with 128-thread CTAs: less to launch on the latency path
+    const uint32_t block = (shape.flavour == FLAVOUR_LDST && shape.only_small && shape.eager_total <= 8192) ? 128 : kLdstThreads;
+
+    if (g.plan_only) {  // CPU tests of the host logic: no device, nothing to launch
+        g.last_args = args;
+        g.last_grid = grid;
+        g.last_block = block;
+        g.last_flavour = shape.flavour;
+        return P2P_SUCCESS;
+    }
+    return submit(ops, res, shape, args, grid, block);
 }
 
 int enqueue(bool is_send, const void* buf, size_t count, int dtype, int peer, cudaStream_t stream) {
