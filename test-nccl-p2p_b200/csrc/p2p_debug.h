@@ -14,6 +14,7 @@ extern "C" {
 #define P2P_DEBUG_CTL_STRIDE 0x1000000000ull
 #define P2P_DEBUG_PEER_WINDOW_SHIFT 44         /* rank r's part of a window is "mapped" at base + ((r+1) << 44) */
 P2P_API int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int ctas_tma);
+P2P_API int p2p_debug_plan_disconnect(uint64_t* host_hash, size_t* ctl_bytes);
 P2P_API int p2p_debug_plan_window(uint64_t base, size_t bytes);
 P2P_API int p2p_debug_plan_last(void* args_out, size_t args_bytes, uint32_t* grid, uint32_t* block, int* flavour);
 #ifdef __cplusplus

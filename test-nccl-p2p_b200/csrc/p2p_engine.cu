@@ -1415,6 +1415,18 @@ int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int c
     return P2P_SUCCESS;
 }
 
+// Back to the state between p2p_init and p2p_connect, so that p2p_connect's checks of the peers' blobs
+// (same host, same protocol limits, rank order) can be exercised without a device.
+int p2p_debug_plan_disconnect(uint64_t* host_hash, size_t* ctl_bytes) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.plan_only) return fail(P2P_INVALID_USAGE, "not in plan-only mode");
+    g.connected = false;
+    g.host_hash = host_hash_now();
+    if (host_hash) *host_hash = g.host_hash;
+    if (ctl_bytes) *ctl_bytes = g.ctl_bytes;
+    return P2P_SUCCESS;
+}
+
 // Pretend `base .. base+bytes` is a registered window of this rank (every rank contributing).
 int p2p_debug_plan_window(uint64_t base, size_t bytes) {
     std::lock_guard<std::mutex> lk(g.mu);

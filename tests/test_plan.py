@@ -218,3 +218,45 @@ def test_plan_snapshot():
     assert sorted(now) == sorted(golden)
     for name in golden:
         assert now[name] == golden[name], f"planner output changed for scenario {name}"
+
+
+def test_connect_checks_the_peers_blobs():
+    """p2p_connect refuses ranks on another host (NVLink peer mappings stop at the host; the reference
+    tolerates several hosts, p2p_matrix.cc:78-99), ranks with other protocol limits, and blobs out of order."""
+    code = r'''
+import ctypes, importlib, struct, sys
+sys.path.insert(0, %r)
+p2p = importlib.import_module("test-nccl-p2p_b200")
+L = p2p.lib()
+L.p2p_debug_plan_init.argtypes = [ctypes.c_int] * 5
+L.p2p_debug_plan_disconnect.argtypes = [ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_size_t)]
+assert L.p2p_debug_plan_init(0, 2, 148, 2, 1) == 0
+hh, cb = ctypes.c_uint64(), ctypes.c_size_t()
+assert L.p2p_debug_plan_disconnect(ctypes.byref(hh), ctypes.byref(cb)) == 0
+n = L.p2p_blob_bytes()
+
+def blob(rank, host_hash=hh.value, eager=p2p.get_option("eager_bytes"), pull=p2p.get_option("pull_min_bytes"), magic=0x42325032, nranks=2):
+    # BootBlob: magic, version, rank, nranks, host_hash, pid, device, eager_bytes, pull_min_bytes, ctl_bytes, ...
+    head = struct.pack("<IIiiQiiQqQ", magic, 1, rank, nranks, host_hash, 424242 + rank, rank, eager, pull, cb.value)
+    return head + bytes(n - len(head))
+
+def connect(b0, b1):
+    rc = L.p2p_connect(ctypes.create_string_buffer(b0 + b1, 2 * n))
+    return rc, L.p2p_get_last_error().decode()
+
+rc, why = connect(blob(0), blob(1, host_hash=hh.value ^ 1))
+assert rc == p2p.INVALID_USAGE and "another host" in why, (rc, why)
+rc, why = connect(blob(0), blob(1, eager=12345))
+assert rc == p2p.INVALID_USAGE and "eager_bytes" in why, (rc, why)
+rc, why = connect(blob(0), blob(1, pull=1 << 30))
+assert rc == p2p.INVALID_USAGE and "pull_min_bytes" in why, (rc, why)
+rc, why = connect(blob(1), blob(0))
+assert rc == p2p.INVALID_ARGUMENT and "rank order" in why, (rc, why)
+rc, why = connect(blob(0), blob(1, magic=7))
+assert rc == p2p.INVALID_ARGUMENT and "not a p2p bootstrap blob" in why, (rc, why)
+rc, why = connect(blob(0), blob(1, nranks=3))
+assert rc == p2p.INVALID_ARGUMENT, (rc, why)
+print("refused as expected")
+''' % ROOT
+    out = run([sys.executable, "-c", code], env={"CUDA_VISIBLE_DEVICES": ""}).stdout
+    assert "refused as expected" in out
