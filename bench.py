@@ -337,9 +337,7 @@ def engine_arm(args):
     roof["ctas"] = plan[1]
 
     torch.cuda.synchronize()
-    p2p.finalize()
-    if world > 1:
-        dist.barrier(group=host_group)
+    p2p.finalize((lambda: dist.barrier(group=host_group)) if world > 1 else None)
 
     if rank == 0:
         line = {

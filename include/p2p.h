@@ -110,7 +110,17 @@ P2P_API int p2p_export(void* blob);
  * enables peer access.  Fails with P2P_INVALID_USAGE if ranks span several hosts (NVLink
  * peer mappings do not cross hosts; the reference tolerates it, p2p_matrix.cc:78-99). */
 P2P_API int p2p_connect(const void* all_blobs);
-/* Drain, unmap peers, free engine memory.  User buffers are never freed by the library. */
+/* Teardown is two-phase like bootstrap, because CUDA IPC requires every importer to close its
+ * mapping before the exporter frees the memory:
+ *
+ *     p2p_disconnect();         // drain this rank's device, close every mapping of peer memory
+ *     <barrier over all ranks>
+ *     p2p_finalize();           // free this rank's own regions
+ *
+ * p2p_finalize alone still works (it disconnects first) but then a peer may free memory this
+ * rank has mapped, or the reverse; p2p_finalize_mpi in p2p_mpi.h and finalize() of the Python
+ * binding run the three steps.  User buffers are never freed by the library. */
+P2P_API int p2p_disconnect(void);
 P2P_API int p2p_finalize(void);
 P2P_API int p2p_rank(void);
 P2P_API int p2p_nranks(void);
@@ -176,9 +186,10 @@ P2P_API int p2p_get_option(const char* name, long long* value);
 P2P_API int p2p_query_plan(size_t bytes, int peer, int* path, int* nblocks);
 
 /* ---- verification support: the reference sends zeros and never reads recv_buff
- *      (p2p_matrix.cc:129-130); parity needs a pattern.  Byte i of (seed, rank, iter) is
- *      byte (i & 7) of splitmix64(seed ^ rank<<48 ^ iter<<24 … ) — see oracle/pattern.h for
- *      the CPU restatement these kernels are tested against. ---- */
+ *      (p2p_matrix.cc:129-130); parity needs a pattern.  With mix = the splitmix64 finaliser and
+ *      G = 0x9E3779B97F4A7C15:  key = mix(seed + G*(rank+1)) ^ mix(iter + 0xD1B54A32D192ED03),
+ *      word(w) = mix(key + G*(w+1)), and byte i of the buffer is little-endian byte (i & 7) of
+ *      word(i >> 3).  oracle/pattern.h is the CPU restatement these kernels are tested against. ---- */
 P2P_API int p2p_pattern_fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter,
                              p2p_stream_t stream);
 /* Counts bytes of `buf` that differ from the pattern; synchronises `stream`.  Also returns

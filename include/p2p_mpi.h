@@ -78,4 +78,15 @@ static inline int p2p_register_mpi(MPI_Comm comm, void* buf, size_t bytes, int* 
     return rc;
 }
 
+/* Collective teardown: close every mapping of peer memory, wait for all ranks to have done so,
+ * then free this rank's own regions (stands in for ncclCommDestroy, p2p_matrix.cc:270). */
+static inline int p2p_finalize_mpi(MPI_Comm comm) {
+    int rc = p2p_disconnect();
+    int brc = MPI_Barrier(comm);  /* reached even if the disconnect failed: peers are waiting in it */
+    int frc = p2p_finalize();
+    if (rc != P2P_SUCCESS) return rc;
+    if (brc != MPI_SUCCESS) return P2P_SYSTEM_ERROR;
+    return frc;
+}
+
 #endif /* B200_P2P_MPI_H */

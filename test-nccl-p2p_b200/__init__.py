@@ -31,7 +31,7 @@ PATH_AUTO, PATH_LDST, PATH_TMA, PATH_CE, PATH_EAGER, PATH_PULL = 0, 1, 2, 3, 4, 
 
 # every symbol include/p2p.h declares; tests check the library exports exactly these
 SYMBOLS = [
-    "p2p_init", "p2p_blob_bytes", "p2p_export", "p2p_connect", "p2p_finalize", "p2p_rank", "p2p_nranks",
+    "p2p_init", "p2p_blob_bytes", "p2p_export", "p2p_connect", "p2p_disconnect", "p2p_finalize", "p2p_rank", "p2p_nranks",
     "p2p_register_blob_bytes", "p2p_register_export", "p2p_register_import", "p2p_deregister",
     "p2p_mem_alloc", "p2p_mem_free", "p2p_send", "p2p_recv", "p2p_group_start", "p2p_group_end", "p2p_alltoall",
     "p2p_get_error_string", "p2p_get_last_error", "p2p_get_async_error", "p2p_set_option", "p2p_get_option",
@@ -66,6 +66,7 @@ def lib() -> ctypes.CDLL:
         "p2p_blob_bytes": (sz, []),
         "p2p_export": (i32, [vp]),
         "p2p_connect": (i32, [vp]),
+        "p2p_disconnect": (i32, []),
         "p2p_finalize": (i32, []),
         "p2p_rank": (i32, []),
         "p2p_nranks": (i32, []),
@@ -162,8 +163,16 @@ def init(rank: int, nranks: int, device: int, allgather: Allgather = _single) ->
     check(L.p2p_connect(joined))
 
 
-def finalize() -> None:
-    check(lib().p2p_finalize())
+def finalize(barrier: Optional[Callable[[], None]] = None) -> None:
+    """p2p_disconnect, a barrier over all ranks (pass one when nranks > 1), p2p_finalize: every rank closes
+    its mappings of peer memory before any rank frees what it exported."""
+    L = lib()
+    rc = L.p2p_disconnect()
+    if barrier is not None:
+        barrier()
+    frc = L.p2p_finalize()
+    check(rc)
+    check(frc)
 
 
 def register(ptr: int, nbytes: int, allgather: Allgather = _single) -> int:

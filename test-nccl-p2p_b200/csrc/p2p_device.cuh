@@ -59,17 +59,31 @@ struct alignas(8) OpDesc {
     uint32_t first_block;
     uint32_t nblocks;
     uint32_t peer;
+    uint32_t flags;      // OPF_*
+    uint32_t pad;
 };
+
+enum OpFlags : uint32_t {
+    OPF_EARLY_POST = 1,  // OP_POST of a send: the word may be published before griddepcontrol.wait when the kernel
+                         // that is still running ahead of this one is the engine's own (token check, see pdl_*)
+};
+
+constexpr uint32_t kPdlLaunched = 1;     // launched with programmatic stream serialisation: griddepcontrol.wait applies
+constexpr uint32_t kPdlLateTrigger = 2;  // mover CTAs let the next kernel in only once their copy loop is done
+constexpr int kTokenSlots = 64;
 
 struct GroupHdr {
     uint32_t nops;
     uint32_t n_ctrl;         // OP_POST ops served by the control CTA (block 0), or 0: no control CTA
-    uint32_t reserved;
+    uint32_t my_token;       // identifies this launch in tokens[] (0: none)
     uint32_t tma_chunk;      // bytes per cp.async.bulk (TMA flavour)
     uint32_t tma_stages;
-    uint32_t pdl;            // launched with programmatic stream serialisation
+    uint32_t pdl;            // kPdl* bits
     uint64_t timeout_ns;
     uint32_t* async_err;     // host-mapped word; first error wins
+    uint32_t* tokens;        // local u32[kTokenSlots]: which engine launches have passed their griddepcontrol.wait
+    uint32_t prev_token;     // the engine launch enqueued right before this one on the same stream (0: unknown)
+    uint32_t pad;
 };
 
 template <int MAXOPS>
@@ -130,14 +144,44 @@ __device__ __forceinline__ void report_error(const GroupHdr& h, uint32_t code) {
     if (h.async_err) atomicCAS_system(h.async_err, 0u, code);
 }
 
-// Programmatic dependent launch: let the next kernel of the stream get resident while this one
-// runs, and hold this one until everything before it in the stream has completed.  Nothing that
-// depends on earlier stream work (user buffers, flags of earlier messages) is touched before.
-__device__ __forceinline__ void pdl_prologue(const GroupHdr& h) {
-    if (h.pdl) {
-        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        asm volatile("griddepcontrol.wait;" ::: "memory");
+// Programmatic dependent launch.  pdl_wait holds a kernel until everything before it in the stream has
+// completed; nothing that depends on earlier stream work (user buffers) is touched before it — what a role
+// may do earlier is poll its own flags and, for a send whose source the kernel ahead cannot be writing, publish
+// where the payload lies (OPF_EARLY_POST).  pdl_trigger lets the next kernel of the stream become resident:
+// the control CTA and the flag-only roles do it at once, mover CTAs after their copy loop (kPdlLateTrigger),
+// so that the next kernel's CTAs arrive as this one's retire instead of crowding the SMs while it runs.
+__device__ __forceinline__ void publish_token(const GroupHdr& h);
+__device__ __forceinline__ void pdl_wait(const GroupHdr& h) {
+    if (h.pdl & kPdlLaunched) asm volatile("griddepcontrol.wait;" ::: "memory");
+    publish_token(h);
+}
+__device__ __forceinline__ void pdl_trigger(const GroupHdr& h) {
+    if (h.pdl & kPdlLaunched) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_trigger_early(const GroupHdr& h) {
+    if ((h.pdl & (kPdlLaunched | kPdlLateTrigger)) == kPdlLaunched) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_trigger_late(const GroupHdr& h) {
+    if ((h.pdl & (kPdlLaunched | kPdlLateTrigger)) == (kPdlLaunched | kPdlLateTrigger)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Block 0 announces, once past its wait, that launch `my_token` is the one running on its stream
+// (called from pdl_wait: the store never precedes the wait).
+__device__ __forceinline__ void publish_token(const GroupHdr& h) {
+    if (h.my_token && h.tokens && blockIdx.x == 0 && threadIdx.x == 0) {
+        asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(h.tokens + (h.my_token % kTokenSlots)), "r"(h.my_token) : "memory");
+        __threadfence();
     }
+}
+// Is the engine launch enqueued right before this one on this stream past its wait (and this kernel therefore
+// running ahead of its completion, with everything older in the stream complete)?
+__device__ __forceinline__ bool predecessor_is_ours(const GroupHdr& h) {
+    return (h.pdl & kPdlLaunched) && h.prev_token && h.tokens &&
+           ld_volatile_u32(h.tokens + (h.prev_token % kTokenSlots)) == h.prev_token;
 }
 
 // Poll helper.  `pred(value)` decides; returns false on timeout.
@@ -252,8 +296,8 @@ __host__ __device__ __forceinline__ uint64_t make_post_word(uint64_t seq, uint32
 }
 
 // One control thread: publish a post word, then wait for the matching completion flag.
-__device__ __forceinline__ void post_and_wait(const GroupHdr& h, const OpDesc& op) {
-    st_release_sys((uint64_t*)op.f_signal, op.word);
+__device__ __forceinline__ void post_and_wait(const GroupHdr& h, const OpDesc& op, bool already_posted = false) {
+    if (!already_posted) st_release_sys((uint64_t*)op.f_signal, op.word);
     uint64_t v;
     const uint64_t want = op.seq;
     if (!spin_flag((const uint64_t*)op.f_wait, h.timeout_ns, v, [want](uint64_t x) { return x == want; }))
@@ -282,16 +326,24 @@ __device__ __forceinline__ uint8_t* push_wait_post(const GroupHdr& h, const OpDe
         *smem_slot = dst;
     }
     __syncthreads();
+    pdl_wait(h);  // the handshake above touched flags only; the payload is read from here on
     return (uint8_t*)(*smem_slot);
 }
 
-// After this CTA's accesses: the last CTA of the op to get here publishes completion.
-__device__ __forceinline__ void movers_signal(const OpDesc& op, uint64_t flag) {
+// After this CTA's accesses: the last CTA of the op to get here publishes completion.  Before that it
+// zeroes the local slot the op's tagged word arrived in (`consumed`): every CTA of the op has read it by then,
+// and a word left behind could be taken for that of the message 65536 sequence numbers later, which carries
+// the same 16-bit tag (the slot's other users may all have been of the other protocol and never rewritten it).
+__device__ __forceinline__ void movers_signal(const GroupHdr& h, const OpDesc& op, uint64_t flag, uint64_t consumed) {
     __syncthreads();
+    pdl_trigger_late(h);
     if (threadIdx.x == 0) {
         fence_sys();  // this CTA's peer accesses are performed before the counter moves
         const uint32_t old = atomicInc((uint32_t*)op.arrive, op.nblocks - 1);
-        if (old == op.nblocks - 1) st_release_sys((uint64_t*)flag, op.seq);  // release = fence + store
+        if (old == op.nblocks - 1) {
+            if (consumed) *(volatile uint64_t*)consumed = 0;
+            st_release_sys((uint64_t*)flag, op.seq);  // release = fence + store
+        }
     }
 }
 
@@ -308,13 +360,19 @@ __device__ __forceinline__ const uint8_t* recv_adaptive(const GroupHdr& h, const
         *smem_slot = v;
     }
     __syncthreads();
+    pdl_wait(h);  // only flags so far; from here on this rank's buffer is written (or offered to the sender)
     const uint64_t v = *smem_slot;
     if (v == 0) return nullptr;
     const uint32_t win = (uint32_t)(v >> 40) & 0xffu;
     if (win == kWinPushPlease) {
-        if (part == 0 && threadIdx.x == 0) {
-            if (op.word) post_and_wait(h, op);
-            else report_error(h, AERR_BAD_WINDOW);  // neither side's buffer is registered
+        if (threadIdx.x == 0) {
+            if (part == 0) {
+                if (op.word) post_and_wait(h, op);
+                else report_error(h, AERR_BAD_WINDOW);  // neither side's buffer is registered
+            }
+            // every CTA of the op has read the sender's word: the last one through clears the slot (see movers_signal)
+            const uint32_t old = atomicInc((uint32_t*)op.arrive, op.nblocks - 1);
+            if (old == op.nblocks - 1) *(volatile uint64_t*)op.f_wait2 = 0;
         }
         return nullptr;
     }
@@ -427,11 +485,20 @@ __device__ __forceinline__ const OpDesc* find_op(const GroupHdr& h, const OpDesc
 
 // Control CTA: thread t serves the t-th OP_POST of the group.
 __device__ __forceinline__ void run_ctrl(const GroupHdr& h, const OpDesc* ops) {
+    const OpDesc* mine = nullptr;
     uint32_t seen = 0;
     for (uint32_t i = 0; i < h.nops; ++i) {
         if (ops[i].kind != OP_POST) continue;
-        if (seen++ == threadIdx.x) { post_and_wait(h, ops[i]); return; }
+        if (seen++ == threadIdx.x) { mine = &ops[i]; break; }
     }
+    bool posted = false;
+    if (mine && (mine->flags & OPF_EARLY_POST) && predecessor_is_ours(h)) {
+        st_release_sys((uint64_t*)mine->f_signal, mine->word);
+        posted = true;
+    }
+    pdl_wait(h);
+    pdl_trigger(h);  // the control CTA only waits on flags: the next kernel may come in at once
+    if (mine) post_and_wait(h, *mine, posted);
 }
 
 // What a mover CTA has to copy once its role has been resolved.
@@ -439,6 +506,7 @@ struct CopyJob {
     uint8_t* dst;
     const uint8_t* src;
     uint64_t signal;     // flag the last CTA publishes afterwards (0: none)
+    uint64_t consumed;   // local slot the op's tagged word arrived in, zeroed by that last CTA
     const OpDesc* op;
     uint32_t part;
     bool is_push;        // destination is peer memory (the TMA flavour stages these)
@@ -450,7 +518,9 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
     const uint32_t bid = blockIdx.x;
     if (h.n_ctrl && bid == 0) { run_ctrl(h, ops); return false; }
     const OpDesc* op = find_op(h, ops, bid);
-    if (!op) return false;
+    if (!op) { pdl_wait(h); return false; }
+    if (op->kind != OP_PUSH && op->kind != OP_RECV_ADAPT) pdl_wait(h);  // those two shake hands first
+    pdl_trigger_early(h);
     const uint32_t part = bid - op->first_block;
     job.op = op;
     job.part = part;
@@ -460,17 +530,20 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
             job.dst = push_wait_post(h, *op, part, slot);
             job.src = (const uint8_t*)op->local;
             job.signal = op->f_signal;
+            job.consumed = op->f_wait;
             job.is_push = true;
             return job.dst != nullptr;
         case OP_COPY:
             job.dst = (uint8_t*)op->aux;
             job.src = (const uint8_t*)op->local;
             job.signal = 0;
+            job.consumed = 0;
             return true;
         case OP_RECV_ADAPT:
             job.src = recv_adaptive(h, *op, part, slot);
             job.dst = (uint8_t*)op->local;
             job.signal = op->f_signal2;
+            job.consumed = op->f_wait2;
             return job.src != nullptr;
         case OP_SEND_LL: ll_send(h, *op, part, slot); return false;
         case OP_RECV_LL: ll_recv(h, *op, part); return false;

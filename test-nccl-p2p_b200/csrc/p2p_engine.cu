@@ -112,9 +112,17 @@ struct Options {
     long long tma_min_bytes = -1;  // auto: pushes at or above this use the TMA flavour (-1 never)
     long long self_tma_min_bytes = 32 << 20;  // auto: local copies at or above this use the TMA flavour (-1 never)
     long long pdl = 1;             // programmatic dependent launch: 0 never, 1 eager-only and local-copy groups (where it
-                                   // measured faster), 2 every group (push/pull kernels measured slower with it)
+                                   // measured faster), 2 every group with the trigger at kernel entry (push/pull kernels
+                                   // measured slower with it), 3 every group, mover CTAs trigger after their copy loop
+    long long early_post = 0;      // with pdl 3: a send offered for pulling is published before the kernel ahead of it on the
+                                   // stream has retired, when that kernel is the engine's own and does not write the payload
     long long loopback = 0;        // 1: a send to oneself goes through the wire protocol instead of a plain copy (tests)
-    long long bidir_push = 1;      // a large send whose group also receives a large message from that peer pushes
+    long long bidir_push = 1;      // a lone large send pushes instead of offering a pull when its group also holds a large
+                                   // receive: 0 never, 1 from that same peer (pairwise exchange), 2 from any peer (ring),
+                                   // 3 as 2 and also with several large sends in the group (all-pairs)
+    long long pull_total = 64;     // CTAs all pulls of one group share (each flow gets pull_total / flows, at least fan_min)
+    long long push_total = 64;     // the same for pushes (each flow at most 32)
+    long long fan_min = 8;
     long long ce_min_bytes = -1;   // experimental, off: a send that is alone in its group and at least this large goes through
                                    // the copy engine when the receiver's host has already said where to.  Measured on 2xB200
                                    // it loses to the pull kernel (256 MiB: 708 vs 726 GB/s streamed, 496 vs 368 us per
@@ -157,6 +165,15 @@ struct Engine {
     cudaEvent_t ce_join[P2P_MAX_RANKS] = {};
     cudaEvent_t ce_fork = nullptr;
     long long stat_launches = 0, stat_ce_copies = 0;
+    // what the last launched group looked like (bench.py reports the kernel that actually ran, not a forecast)
+    long long last_stat[12] = {};
+    uint32_t* tokens = nullptr;                 // device u32[kTokenSlots], see publish_token()
+    uint32_t launch_counter = 0;
+    struct StreamLast {
+        uint32_t token = 0;
+        std::vector<std::pair<const uint8_t*, size_t>> writes;  // user memory that launch writes (its receives)
+    };
+    std::map<cudaStream_t, StreamLast> stream_last;
 
     // plan-only mode (p2p_debug.h): groups are resolved exactly as usual but captured instead of launched
     bool plan_only = false;
@@ -237,6 +254,75 @@ long long env_ll(const char* name, long long dflt) {
 int check_ready() {
     if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
     if (!g.connected) return fail(P2P_INVALID_USAGE, "p2p_connect has not been called");
+    return P2P_SUCCESS;
+}
+
+
+// ---- options: one table, one set of range checks for the environment and for p2p_set_option ----
+
+using OptionSlot = long long Options::*;
+struct OptionSpec {
+    const char* name;
+    const char* env;       // nullptr: not settable from the environment
+    OptionSlot slot;
+    long long lo, hi;
+};
+
+const OptionSpec kOptionSpecs[] = {
+    {"path", "P2P_PATH", &Options::path, 0, 3},
+    {"nblocks", "P2P_NBLOCKS", &Options::nblocks, 0, 4096},
+    {"self_nblocks", "P2P_SELF_NBLOCKS", &Options::self_nblocks, 0, 4096},
+    {"pull_nblocks", "P2P_PULL_NBLOCKS", &Options::pull_nblocks, 0, 4096},
+    {"eager_nblocks", "P2P_EAGER_NBLOCKS", &Options::eager_nblocks, 0, 4096},
+    {"eager_bytes", "P2P_EAGER_BYTES", &Options::eager_bytes, 0, 1 << 20},
+    {"pull_min_bytes", "P2P_PULL_MIN_BYTES", &Options::pull_min_bytes, -1, 1ll << 40},
+    {"timeout_ms", "P2P_TIMEOUT_MS", &Options::timeout_ms, 1, 3600ll * 1000},
+    {"tma_chunk", "P2P_TMA_CHUNK", &Options::tma_chunk, 1024, 128 * 1024},
+    {"tma_stages", "P2P_TMA_STAGES", &Options::tma_stages, 2, kTmaMaxStages},
+    {"tma_min_bytes", "P2P_TMA_MIN_BYTES", &Options::tma_min_bytes, -1, 1ll << 40},
+    {"self_tma_min_bytes", "P2P_SELF_TMA_MIN_BYTES", &Options::self_tma_min_bytes, -1, 1ll << 40},
+    {"pdl", "P2P_PDL", &Options::pdl, 0, 3},
+    {"early_post", "P2P_EARLY_POST", &Options::early_post, 0, 1},
+    {"loopback", "P2P_LOOPBACK", &Options::loopback, 0, 1},
+    {"bidir_push", "P2P_BIDIR_PUSH", &Options::bidir_push, 0, 3},
+    {"pull_total", "P2P_PULL_TOTAL", &Options::pull_total, 1, 1024},
+    {"push_total", "P2P_PUSH_TOTAL", &Options::push_total, 1, 1024},
+    {"fan_min", "P2P_FAN_MIN", &Options::fan_min, 1, 64},
+    {"ce_min_bytes", "P2P_CE_MIN_BYTES", &Options::ce_min_bytes, -1, 1ll << 40},
+    {"ce_wait_us", "P2P_CE_WAIT_US", &Options::ce_wait_us, 0, 10000000},
+};
+
+const OptionSpec* find_option(const char* name) {
+    for (const OptionSpec& sp : kOptionSpecs)
+        if (!strcmp(sp.name, name)) return &sp;
+    return nullptr;
+}
+
+// Range of one value, and the constraints that tie options together, checked on the set `o` would become.
+int validate_option(const OptionSpec& sp, long long value, const Options& o, const char* source) {
+    if (value < sp.lo || value > sp.hi)
+        return fail(P2P_INVALID_ARGUMENT, "%s%s = %lld is outside [%lld, %lld]", source, sp.name, value, sp.lo, sp.hi);
+    Options t = o;
+    t.*(sp.slot) = value;
+    if (t.tma_chunk % 16)
+        return fail(P2P_INVALID_ARGUMENT, "%stma_chunk = %lld is not a multiple of 16 (cp.async.bulk alignment)", source, t.tma_chunk);
+    if (t.tma_chunk * t.tma_stages > 200 * 1024)
+        return fail(P2P_INVALID_ARGUMENT, "%stma ring %lld x %lld bytes exceeds 200 KiB of shared memory", source, t.tma_stages, t.tma_chunk);
+    return P2P_SUCCESS;
+}
+
+// Options from the environment, through the same checks as p2p_set_option.
+int read_env_options(Options& o) {
+    for (const OptionSpec& sp : kOptionSpecs) {
+        if (!sp.env) continue;
+        const long long v = env_ll(sp.env, o.*(sp.slot));
+        if (v == o.*(sp.slot)) continue;
+        char source[64];
+        snprintf(source, sizeof source, "%s: ", sp.env);
+        int rc = validate_option(sp, v, o, source);
+        if (rc) return rc;
+        o.*(sp.slot) = v;
+    }
     return P2P_SUCCESS;
 }
 
@@ -354,9 +440,10 @@ inline int mover_ctas(size_t nbytes, int flavour, bool self, bool pull, int fano
     long long cap;
     if (self) cap = g.opt.self_nblocks ? g.opt.self_nblocks : (long long)g.sm_count;  // 1 CTA per SM beat 2 (6.17 vs 6.02 TB/s)
     // one flow wants many CTAs in flight (pull: 64 -> 725 GB/s, 32 -> 610); several concurrent flows per GPU
-    // want few each (all-pairs on 8 GPUs: 8 CTAs per flow 4.83 TB/s, 32 per flow 4.58)
-    else if (pull) cap = g.opt.pull_nblocks ? g.opt.pull_nblocks : (fanout >= 3 ? 8 : fanout == 2 ? 32 : 64);
-    else cap = g.opt.nblocks ? g.opt.nblocks : (fanout >= 3 ? 8 : 32);
+    // want few each (all-pairs on 8 GPUs: 8 CTAs per flow 4.83 TB/s, 32 per flow 4.58) but not fewer in total
+    // than one flow would get (3 flows of 8 CTAs on 4 GPUs: 1.73 TB/s, of 32: 2.43): the flows share a total
+    else if (pull) cap = g.opt.pull_nblocks ? g.opt.pull_nblocks : std::max(g.opt.fan_min, g.opt.pull_total / std::max(fanout, 1));
+    else cap = g.opt.nblocks ? g.opt.nblocks : std::min<long long>(32, std::max(g.opt.fan_min, g.opt.push_total / std::max(fanout, 1)));
     return (int)std::max<size_t>(1, std::min<size_t>(tiles, (size_t)cap));
 }
 
@@ -468,11 +555,17 @@ int resolve_protocols(const std::vector<PendingOp>& ops, const std::vector<int>&
             // exchange (one large send, and a large receive from that same peer in the group), where two pushes
             // interfere less than two pulls (1.32 vs 1.24 TB/s between two B200s).  With several large sends in
             // the group (fan-out, all-pairs) pulls with few CTAs win again (4.83 vs 4.28 TB/s on 8 GPUs).
-            bool also_receiving = false;
+            bool from_same_peer = false;
             for (size_t j = 0; j < ops.size(); ++j)
-                if (!ops[j].is_send && ops[j].peer == op.peer && partner[j] < 0 && is_large(ops[j].nbytes)) also_receiving = true;
-            const bool pairwise = also_receiving && shape.n_large_sends == 1 && g.opt.bidir_push;
-            r.pull_send = r.registered && !pairwise && g.opt.path != 2 && g.opt.path != 1;
+                if (!ops[j].is_send && ops[j].peer == op.peer && partner[j] < 0 && is_large(ops[j].nbytes)) from_same_peer = true;
+            bool push_instead = false;
+            switch (g.opt.bidir_push) {
+                case 1: push_instead = from_same_peer && shape.n_large_sends == 1; break;
+                case 2: push_instead = shape.n_large_recvs > 0 && shape.n_large_sends == 1; break;
+                case 3: push_instead = shape.n_large_recvs > 0; break;
+                default: break;
+            }
+            r.pull_send = r.registered && !push_instead && g.opt.path != 2 && g.opt.path != 1;
         }
         if (op.is_send && !(r.proto == PROTO_LARGE && r.pull_send) && push_flavour(op.nbytes) == 2) shape.flavour = FLAVOUR_TMA;
     }
@@ -577,7 +670,7 @@ void size_roles(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, G
 }
 
 // Fills one role's descriptor: which flags it polls and writes, in whose control region.
-void describe_role(const PendingOp& op, const Resolved& r, const PendingOp* copy_partner, OpDesc& d) {
+void describe_role(const PendingOp& op, const Resolved& r, const PendingOp* copy_partner, bool may_post_early, OpDesc& d) {
     const int me = g.rank, p = op.peer;
     uint8_t* my = g.ctl;
     uint8_t* theirs = g.peer_ctl[p];
@@ -615,6 +708,7 @@ void describe_role(const PendingOp& op, const Resolved& r, const PendingOp* copy
         }
     } else if (r.proto == PROTO_LARGE && r.pull_send) {
         d.kind = OP_POST;  // publish where my payload lies, wait until it has been read
+        d.flags = may_post_early ? OPF_EARLY_POST : 0;
         d.word = make_post_word(seq, r.win, r.off);
         d.f_signal = (uint64_t)&peer_section(theirs, me)->pull_post[seq % kRing];
         d.f_wait = (uint64_t)&peer_section(my, p)->pull_done[seq % kRing];
@@ -636,6 +730,28 @@ void describe_role(const PendingOp& op, const Resolved& r, const PendingOp* copy
 uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolved>& res, const std::vector<int>& partner,
                     const GroupShape& shape, GroupArgs& args) {
     memset(&args, 0, sizeof args);
+    // Which engine launch precedes this one on its stream, and may this one's sends be offered before that
+    // launch has retired?  Only when the whole group sits on one stream (no event waits in front of the kernel)
+    // and the payload does not overlap anything the launch ahead receives into.
+    cudaStream_t launch_stream = ops[0].stream;
+    bool one_stream = true;
+    for (const PendingOp& op : ops) one_stream = one_stream && op.stream == launch_stream;
+    const Engine::StreamLast* prev = nullptr;
+    if (one_stream) {
+        auto it = g.stream_last.find(launch_stream);
+        if (it != g.stream_last.end()) prev = &it->second;
+    }
+    auto early_ok = [&](const PendingOp& op) {
+        if (!prev || !g.opt.early_post || g.opt.pdl != 3) return false;
+        const uint8_t* b = (const uint8_t*)op.buf;
+        for (const auto& w : prev->writes)
+            if (b < w.first + w.second && w.first < b + op.nbytes) return false;
+        return true;
+    };
+    args.h.tokens = g.tokens;
+    if (++g.launch_counter == 0) ++g.launch_counter;
+    args.h.my_token = g.launch_counter;
+    args.h.prev_token = prev ? prev->token : 0;
     args.h.tma_chunk = (uint32_t)g.opt.tma_chunk;
     args.h.tma_stages = (uint32_t)g.opt.tma_stages;
     args.h.timeout_ns = (uint64_t)g.opt.timeout_ms * 1000000ull;
@@ -653,7 +769,7 @@ uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolve
             else cls = op.is_send ? (r.ce ? -1 : r.pull_send ? 0 : 4) : 3;
             if (cls != pass) continue;
             OpDesc& d = args.ops[args.h.nops++];
-            describe_role(op, r, r.proto == PROTO_COPY ? &ops[(size_t)partner[i]] : nullptr, d);
+            describe_role(op, r, r.proto == PROTO_COPY ? &ops[(size_t)partner[i]] : nullptr, op.is_send && early_ok(op), d);
             if (d.kind != OP_POST) {
                 d.first_block = next_block;
                 next_block += d.nblocks;
@@ -665,7 +781,18 @@ uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolve
         const uint32_t k = args.ops[i].kind;
         if (k == OP_POST || k == OP_PUSH || k == OP_RECV_ADAPT) light = false;
     }
-    args.h.pdl = (g.opt.pdl == 2 || (g.opt.pdl == 1 && light && !shape.any_ce)) ? 1 : 0;
+    if (shape.any_ce) args.h.pdl = 0;
+    else if (g.opt.pdl >= 2) args.h.pdl = kPdlLaunched | (g.opt.pdl == 3 ? kPdlLateTrigger : 0);
+    else args.h.pdl = (g.opt.pdl == 1 && light) ? kPdlLaunched : 0;
+    // remember this launch as the latest on its stream; the other streams of the group now end in an event wait
+    Engine::StreamLast mine;
+    mine.token = args.h.my_token;
+    for (const PendingOp& op : ops) {
+        if (!op.is_send && op.nbytes) mine.writes.emplace_back((const uint8_t*)op.buf, op.nbytes);
+        if (op.stream != launch_stream) g.stream_last.erase(op.stream);
+    }
+    if (g.stream_last.size() > 256) g.stream_last.clear();  // streams come and go; forgetting only costs an early post
+    g.stream_last[launch_stream] = std::move(mine);
     return next_block;
 }
 
@@ -751,6 +878,25 @@ int launch_pending() {
     // small eager-only groups run with 128-thread CTAs: less to launch on the latency path
     const uint32_t block = (shape.flavour == FLAVOUR_LDST && shape.only_small && shape.eager_total <= 8192) ? 128 : kLdstThreads;
 
+    {
+        long long* st = g.last_stat;
+        for (int i = 0; i < 12; ++i) st[i] = 0;
+        st[0] = shape.flavour; st[1] = grid; st[2] = shape.flavour == FLAVOUR_TMA ? kTmaThreads : block; st[11] = args.h.pdl;
+        for (uint32_t i = 0; i < args.h.nops; ++i) {
+            const OpDesc& d = args.ops[i];
+            switch (d.kind) {
+                case OP_PUSH: st[3]++; st[4] += d.nblocks; break;
+                case OP_RECV_ADAPT: st[6]++; st[7] += d.nblocks; break;
+                case OP_SEND_LL: case OP_RECV_LL: st[8]++; break;
+                case OP_COPY: st[9] += d.nblocks; break;
+                default: break;
+            }
+        }
+        for (size_t i = 0; i < ops.size(); ++i) {
+            if (ops[i].is_send && res[i].proto == PROTO_LARGE && res[i].pull_send && !res[i].ce) st[5]++;
+            if (res[i].ce) st[10]++;
+        }
+    }
     if (g.plan_only) {  // CPU tests of the host logic: no device, nothing to launch
         g.last_args = args;
         g.last_grid = grid;
@@ -772,6 +918,10 @@ int enqueue(bool is_send, const void* buf, size_t count, int dtype, int peer, cu
     if (nbytes > kPostOffMask) return fail(P2P_INVALID_ARGUMENT, "message of %zu bytes exceeds the 512 GiB limit", nbytes);
     if (nbytes && !buf) return fail(P2P_INVALID_ARGUMENT, "null buffer with count %zu", count);
     std::lock_guard<std::mutex> lk(g.mu);
+    // after a device-side timeout counters and flag rings are no longer consistent: nothing more is issued
+    if (g.async_err_host && *(volatile uint32_t*)g.async_err_host != AERR_NONE)
+        return fail(P2P_REMOTE_ERROR, "the engine is in an error state (device code %u, see p2p_get_async_error); "
+                    "no further transfers are issued until p2p_finalize", *(volatile uint32_t*)g.async_err_host);
     g.group_ops.push_back(PendingOp{is_send, buf, nbytes, peer, stream});
     if (g.group_depth == 0) return launch_pending();
     return P2P_SUCCESS;
@@ -861,25 +1011,10 @@ int p2p_init(int rank, int nranks, int device) {
 
     Options& o = g.opt;
     o = Options();
-    o.path = env_ll("P2P_PATH", o.path);
-    o.nblocks = env_ll("P2P_NBLOCKS", o.nblocks);
-    o.self_nblocks = env_ll("P2P_SELF_NBLOCKS", o.self_nblocks);
-    o.eager_bytes = env_ll("P2P_EAGER_BYTES", o.eager_bytes);
-    o.timeout_ms = env_ll("P2P_TIMEOUT_MS", o.timeout_ms);
-    o.pull_nblocks = env_ll("P2P_PULL_NBLOCKS", o.pull_nblocks);
-    o.eager_nblocks = env_ll("P2P_EAGER_NBLOCKS", o.eager_nblocks);
-    o.pull_min_bytes = env_ll("P2P_PULL_MIN_BYTES", o.pull_min_bytes);
-    o.pdl = env_ll("P2P_PDL", o.pdl);
-    o.loopback = env_ll("P2P_LOOPBACK", o.loopback);
-    o.bidir_push = env_ll("P2P_BIDIR_PUSH", o.bidir_push);
-    o.ce_min_bytes = env_ll("P2P_CE_MIN_BYTES", o.ce_min_bytes);
-    o.ce_wait_us = env_ll("P2P_CE_WAIT_US", o.ce_wait_us);
-    o.tma_chunk = env_ll("P2P_TMA_CHUNK", o.tma_chunk);
-    o.tma_stages = env_ll("P2P_TMA_STAGES", o.tma_stages);
-    o.tma_min_bytes = env_ll("P2P_TMA_MIN_BYTES", o.tma_min_bytes);
-    o.self_tma_min_bytes = env_ll("P2P_SELF_TMA_MIN_BYTES", o.self_tma_min_bytes);
-    if (o.eager_bytes < 0 || o.eager_bytes > (1 << 20))
-        return fail(P2P_INVALID_ARGUMENT, "P2P_EAGER_BYTES %lld outside [0, 1 MiB]", o.eager_bytes);
+    {
+        int rc = read_env_options(o);
+        if (rc) return rc;
+    }
 
     // control region: per-peer flag sections, then the eager rings
     g.ll_slot_bytes = (size_t)std::max<long long>(o.eager_bytes, 8) * 2;
@@ -893,6 +1028,10 @@ int p2p_init(int rank, int nranks, int device) {
     CUDA_TRY(cudaMemset(g.arrive, 0, sizeof(uint32_t) * arrive_words));
     CUDA_TRY(cudaMalloc(&g.win_table, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
     CUDA_TRY(cudaMemset(g.win_table, 0, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
+    CUDA_TRY(cudaMalloc(&g.tokens, sizeof(uint32_t) * kTokenSlots));
+    CUDA_TRY(cudaMemset(g.tokens, 0, sizeof(uint32_t) * kTokenSlots));
+    g.launch_counter = 0;
+    g.stream_last.clear();
     CUDA_TRY(cudaMalloc(&g.chk_partials, sizeof(CheckPartial) * (size_t)g.sm_count * 8));
     CUDA_TRY(cudaMalloc(&g.chk_ticket, sizeof(unsigned int)));
     CUDA_TRY(cudaMemset(g.chk_ticket, 0, sizeof(unsigned int)));
@@ -972,6 +1111,17 @@ int p2p_connect(const void* all_blobs) {
         if (b.pull_min_bytes != g.opt.pull_min_bytes)
             return fail(P2P_INVALID_USAGE, "rank %d uses pull_min_bytes=%lld, this rank %lld; they must match", r,
                         (long long)b.pull_min_bytes, g.opt.pull_min_bytes);
+        b.pci_bus_id[sizeof b.pci_bus_id - 1] = '\0';
+        for (int q = 0; q < r; ++q) {
+            BootBlob bq;
+            memcpy(&bq, (const uint8_t*)all_blobs + (size_t)q * kBlobBytes, sizeof bq);
+            bq.pci_bus_id[sizeof bq.pci_bus_id - 1] = '\0';
+            if (b.pci_bus_id[0] && !strcmp(b.pci_bus_id, bq.pci_bus_id))
+                return fail(P2P_INVALID_USAGE,
+                            "ranks %d and %d both drive GPU %s: the engine is one process per GPU (kernels of two ranks that "
+                            "wait for each other's flags cannot share a GPU); launch at most as many ranks as there are GPUs",
+                            q, r, b.pci_bus_id);
+        }
         if (r == g.rank) continue;
         if (b.ctl_bytes != g.ctl_bytes)
             return fail(P2P_INTERNAL_ERROR, "rank %d control region is %llu bytes, mine %zu", r,
@@ -999,23 +1149,11 @@ int p2p_connect(const void* all_blobs) {
     return P2P_SUCCESS;
 }
 
-int p2p_finalize(void) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.inited) return P2P_SUCCESS;
-    if (g.plan_only) {  // nothing was allocated
-        for (int w = 0; w < P2P_MAX_WINDOWS; ++w) g.windows[w] = Window();
-        for (int r = 0; r < P2P_MAX_RANKS; ++r) {
-            g.peer_ctl[r] = nullptr;
-            g.rdv_send_seq[r] = g.rdv_recv_seq[r] = g.ll_send_seq[r] = g.ll_recv_seq[r] = 0;
-        }
-        g.ctl = nullptr;
-        g.arrive = nullptr;
-        g.win_table = nullptr;
-        g.group_ops.clear();
-        g.group_depth = 0;
-        g.plan_only = g.inited = g.connected = false;
-        return P2P_SUCCESS;
-    }
+// Teardown in two steps, because CUDA IPC wants every importer to close its mapping before the exporter
+// frees the memory: p2p_disconnect (drain, close every mapping of peer memory), a barrier supplied by the
+// caller, then p2p_finalize (free this rank's own regions).
+static int disconnect_locked() {
+    if (!g.inited || g.plan_only) return P2P_SUCCESS;
     cudaSetDevice(g.device);
     cudaDeviceSynchronize();
     for (int w = 0; w < P2P_MAX_WINDOWS; ++w) {
@@ -1028,6 +1166,39 @@ int p2p_finalize(void) {
     for (int r = 0; r < g.nranks; ++r) {
         for (auto& kv : g.ipc_cache[r]) cudaIpcCloseMemHandle(kv.second.ptr);
         g.ipc_cache[r].clear();
+        if (r != g.rank) g.peer_ctl[r] = nullptr;
+    }
+    g.connected = false;
+    return P2P_SUCCESS;
+}
+
+int p2p_disconnect(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    return disconnect_locked();
+}
+
+int p2p_finalize(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.inited) return P2P_SUCCESS;
+    if (g.plan_only) {  // nothing was allocated
+        for (int w = 0; w < P2P_MAX_WINDOWS; ++w) g.windows[w] = Window();
+        for (int r = 0; r < P2P_MAX_RANKS; ++r) {
+            g.peer_ctl[r] = nullptr;
+            g.rdv_send_seq[r] = g.rdv_recv_seq[r] = g.ll_send_seq[r] = g.ll_recv_seq[r] = 0;
+        }
+        g.ctl = nullptr;
+        g.arrive = nullptr;
+        g.win_table = nullptr;
+        g.tokens = nullptr;
+        g.stream_last.clear();
+        g.launch_counter = 0;
+        g.group_ops.clear();
+        g.group_depth = 0;
+        g.plan_only = g.inited = g.connected = false;
+        return P2P_SUCCESS;
+    }
+    disconnect_locked();  // a no-op when p2p_disconnect has run
+    for (int r = 0; r < P2P_MAX_RANKS; ++r) {
         g.peer_ctl[r] = nullptr;
         g.rdv_send_seq[r] = g.rdv_recv_seq[r] = g.ll_send_seq[r] = g.ll_recv_seq[r] = 0;
     }
@@ -1046,11 +1217,16 @@ int p2p_finalize(void) {
     cudaFree(g.ctl);
     cudaFree(g.arrive);
     cudaFree(g.win_table);
+    cudaFree(g.tokens);
+    g.tokens = nullptr;
+    g.stream_last.clear();
     cudaFree(g.chk_partials);
     cudaFree(g.chk_ticket);
     cudaFree(g.chk_out);
     cudaFreeHost(g.chk_out_host);
     cudaFreeHost(g.async_err_host);
+    g.async_err_host = nullptr;
+    g.async_err_dev = nullptr;
     if (g.ev_done) cudaEventDestroy(g.ev_done);
     for (cudaEvent_t e : g.ev_pool) cudaEventDestroy(e);
     g.ev_pool.clear();
@@ -1255,58 +1431,25 @@ int p2p_get_async_error(int* result) {
     return P2P_SUCCESS;
 }
 
-static long long* option_slot(const char* name) {
-    Options& o = g.opt;
-    if (!strcmp(name, "path")) return &o.path;
-    if (!strcmp(name, "nblocks")) return &o.nblocks;
-    if (!strcmp(name, "self_nblocks")) return &o.self_nblocks;
-    if (!strcmp(name, "eager_bytes")) return &o.eager_bytes;
-    if (!strcmp(name, "timeout_ms")) return &o.timeout_ms;
-    if (!strcmp(name, "pull_nblocks")) return &o.pull_nblocks;
-    if (!strcmp(name, "eager_nblocks")) return &o.eager_nblocks;
-    if (!strcmp(name, "pull_min_bytes")) return &o.pull_min_bytes;
-    if (!strcmp(name, "pdl")) return &o.pdl;
-    if (!strcmp(name, "loopback")) return &o.loopback;
-    if (!strcmp(name, "bidir_push")) return &o.bidir_push;
-    if (!strcmp(name, "ce_min_bytes")) return &o.ce_min_bytes;
-    if (!strcmp(name, "ce_wait_us")) return &o.ce_wait_us;
-    if (!strcmp(name, "tma_chunk")) return &o.tma_chunk;
-    if (!strcmp(name, "tma_stages")) return &o.tma_stages;
-    if (!strcmp(name, "tma_min_bytes")) return &o.tma_min_bytes;
-    if (!strcmp(name, "self_tma_min_bytes")) return &o.self_tma_min_bytes;
-    return nullptr;
-}
-
 int p2p_set_option(const char* name, long long value) {
     std::lock_guard<std::mutex> lk(g.mu);
     if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
     if (!name) return fail(P2P_INVALID_ARGUMENT, "null option name");
-    long long* slot = option_slot(name);
-    if (!slot) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
-    if (!strcmp(name, "eager_bytes")) {
-        // the rings were sized in p2p_init; the limit can only shrink afterwards, and on every rank alike
-        if (value < 0 || (size_t)value * 2 > g.ll_slot_bytes)
-            return fail(P2P_INVALID_ARGUMENT, "eager_bytes %lld exceeds the ring slot (%zu bytes); set P2P_EAGER_BYTES before p2p_init",
-                        value, g.ll_slot_bytes / 2);
-    } else if (!strcmp(name, "path")) {
-        if (value < 0 || value > 3) return fail(P2P_INVALID_ARGUMENT, "path must be 0..3");
-    } else if (!strcmp(name, "pull_min_bytes")) {
+    const OptionSpec* sp = find_option(name);
+    if (!sp) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
+    if (!strcmp(name, "pull_min_bytes"))
         return fail(P2P_INVALID_USAGE, "pull_min_bytes is agreed between ranks at p2p_connect; set P2P_PULL_MIN_BYTES before p2p_init");
-    } else if (!strcmp(name, "tma_chunk") || !strcmp(name, "tma_stages")) {
-        long long chunk = !strcmp(name, "tma_chunk") ? value : g.opt.tma_chunk;
-        long long stages = !strcmp(name, "tma_stages") ? value : g.opt.tma_stages;
-        if (chunk < 1024 || chunk % 16 || chunk > 128 * 1024 || stages < 2 || stages > kTmaMaxStages ||
-            chunk * stages > 200 * 1024)
-            return fail(P2P_INVALID_ARGUMENT, "tma ring %lld x %lld bytes is not allowed (<= 200 KiB, 2..%d stages)",
-                        stages, chunk, kTmaMaxStages);
-        *slot = value;
+    int rc = validate_option(*sp, value, g.opt, "");
+    if (rc) return rc;
+    // the rings were sized in p2p_init; the limit can only shrink afterwards, and on every rank alike
+    if (!strcmp(name, "eager_bytes") && (size_t)value * 2 > g.ll_slot_bytes)
+        return fail(P2P_INVALID_ARGUMENT, "eager_bytes %lld exceeds the ring slot (%zu bytes); set P2P_EAGER_BYTES before p2p_init",
+                    value, g.ll_slot_bytes / 2);
+    g.opt.*(sp->slot) = value;
+    if ((!strcmp(name, "tma_chunk") || !strcmp(name, "tma_stages")) && !g.plan_only) {
         int n = 1;
         if (occupancy(FLAVOUR_TMA, (int)(g.opt.tma_chunk * g.opt.tma_stages), &n) == cudaSuccess && n >= 1) g.ctas_tma = n;
-        return P2P_SUCCESS;
-    } else if (value < 0 && strcmp(name, "tma_min_bytes") && strcmp(name, "self_tma_min_bytes") && strcmp(name, "ce_min_bytes")) {
-        return fail(P2P_INVALID_ARGUMENT, "option '%s' must be >= 0", name);
     }
-    *slot = value;
     return P2P_SUCCESS;
 }
 
@@ -1317,11 +1460,18 @@ int p2p_get_option(const char* name, long long* value) {
     if (!strcmp(name, "sm_count")) { *value = g.sm_count; return P2P_SUCCESS; }
     if (!strcmp(name, "stat_launches")) { *value = g.stat_launches; return P2P_SUCCESS; }
     if (!strcmp(name, "stat_ce_copies")) { *value = g.stat_ce_copies; return P2P_SUCCESS; }
+    {
+        static const char* const names[12] = {"stat_last_flavour", "stat_last_grid", "stat_last_block", "stat_last_push_ops",
+                                              "stat_last_push_ctas", "stat_last_offer_ops", "stat_last_recv_ops", "stat_last_recv_ctas",
+                                              "stat_last_eager_ops", "stat_last_copy_ctas", "stat_last_ce_ops", "stat_last_pdl"};
+        for (int i = 0; i < 12; ++i)
+            if (!strcmp(name, names[i])) { *value = g.last_stat[i]; return P2P_SUCCESS; }
+    }
     if (!strcmp(name, "ctas_per_sm_ldst")) { *value = g.ctas_ldst; return P2P_SUCCESS; }
     if (!strcmp(name, "ctas_per_sm_tma")) { *value = g.ctas_tma; return P2P_SUCCESS; }
-    long long* slot = option_slot(name);
-    if (!slot) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
-    *value = *slot;
+    const OptionSpec* sp = find_option(name);
+    if (!sp) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
+    *value = g.opt.*(sp->slot);
     return P2P_SUCCESS;
 }
 
@@ -1388,18 +1538,10 @@ int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int c
     g.ctas_tma = ctas_tma;
     Options& o = g.opt;
     o = Options();
-    o.path = env_ll("P2P_PATH", o.path);
-    o.nblocks = env_ll("P2P_NBLOCKS", o.nblocks);
-    o.self_nblocks = env_ll("P2P_SELF_NBLOCKS", o.self_nblocks);
-    o.eager_bytes = env_ll("P2P_EAGER_BYTES", o.eager_bytes);
-    o.pull_nblocks = env_ll("P2P_PULL_NBLOCKS", o.pull_nblocks);
-    o.eager_nblocks = env_ll("P2P_EAGER_NBLOCKS", o.eager_nblocks);
-    o.pull_min_bytes = env_ll("P2P_PULL_MIN_BYTES", o.pull_min_bytes);
-    o.pdl = env_ll("P2P_PDL", o.pdl);
-    o.loopback = env_ll("P2P_LOOPBACK", o.loopback);
-    o.bidir_push = env_ll("P2P_BIDIR_PUSH", o.bidir_push);
-    o.tma_min_bytes = env_ll("P2P_TMA_MIN_BYTES", o.tma_min_bytes);
-    o.self_tma_min_bytes = env_ll("P2P_SELF_TMA_MIN_BYTES", o.self_tma_min_bytes);
+    {
+        int rc = read_env_options(o);
+        if (rc) return rc;
+    }
     // the same layout arithmetic as p2p_init, over made-up base addresses: rank r's control region "lives" at
     // P2P_DEBUG_CTL_BASE + r * P2P_DEBUG_CTL_STRIDE, so tests can tell whose memory a flag address points into
     g.ll_slot_bytes = ((size_t)std::max<long long>(o.eager_bytes, 8) * 2 + 255) & ~(size_t)255;
@@ -1409,8 +1551,12 @@ int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int c
     g.ctl = g.peer_ctl[rank];
     g.arrive = (uint32_t*)0x200000000000ull;
     g.win_table = (uint64_t*)0x300000000000ull;
+    g.tokens = (uint32_t*)0x400000000000ull;
+    g.launch_counter = 0;
+    g.stream_last.clear();
     g.hostbox = nullptr;
     g.async_err_dev = nullptr;
+    g.async_err_host = nullptr;
     g.plan_only = g.inited = g.connected = true;
     return P2P_SUCCESS;
 }

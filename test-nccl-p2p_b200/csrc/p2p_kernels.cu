@@ -13,11 +13,11 @@ template <int MAXOPS>
 __global__ void __launch_bounds__(kLdstThreads, 2)
 p2p_group_kernel_ldst(const __grid_constant__ GroupArgsT<MAXOPS> a) {
     __shared__ uint64_t slot;
-    pdl_prologue(a.h);
     CopyJob job;
     if (!resolve_role(a.h, a.ops, &slot, job)) return;
     copy_bytes(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks);
-    if (job.signal) movers_signal(*job.op, job.signal);
+    if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);
+    else pdl_trigger_late(a.h);
 }
 
 // TMA flavour: 128-thread CTAs, a push is staged global -> shared -> peer global by
@@ -34,7 +34,6 @@ p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
         fence_proxy_async();
     }
     __syncthreads();
-    pdl_prologue(a.h);
     CopyJob job;
     if (!resolve_role(a.h, a.ops, &slot, job)) return;
     // the ring stages pushes and local copies; a pull (peer -> local) keeps the register loop
@@ -42,7 +41,8 @@ p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
         tma_push(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty);
     else
         copy_bytes(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks);
-    if (job.signal) movers_signal(*job.op, job.signal);
+    if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);
+    else pdl_trigger_late(a.h);
 }
 
 cudaError_t configure_kernels(int max_tma_smem) {

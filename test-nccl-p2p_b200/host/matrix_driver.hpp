@@ -761,7 +761,14 @@ int run_main(Backend& be, int argc, char** argv) {
     int gpu_id = placement_device(rank, world_size);  // p2p_matrix.cc:109
     int ndev = 0;
     CUDACHECK(cudaGetDeviceCount(&ndev));
-    if (ndev > 0 && gpu_id >= ndev) gpu_id %= ndev;  // more ranks than GPUs: share (the reference would fail in cudaSetDevice)
+    if (gpu_id >= ndev) {
+        // The reference would fail in cudaSetDevice here.  Sharing a GPU between ranks is refused outright: two ranks
+        // whose kernels wait for each other's flags on one GPU can starve each other for ever.
+        if (rank == 0)
+            printf("Failed: %d ranks on this host but only %d GPU%s; launch at most one rank per GPU\n", world_size, ndev,
+                   ndev == 1 ? "" : "s");
+        exit(EXIT_FAILURE);
+    }
     CUDACHECK(cudaSetDevice(gpu_id));                 // p2p_matrix.cc:119
     be.init(rank, world_size, gpu_id);
 

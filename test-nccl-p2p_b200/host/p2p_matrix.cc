@@ -51,7 +51,7 @@ struct EngineBackend {
             printf("Failed, P2P async error '%s' (%s)\n", p2p_get_error_string(aerr), p2p_get_last_error());
             exit(EXIT_FAILURE);
         }
-        P2PCHECK(p2p_finalize());  // ncclCommDestroy, p2p_matrix.cc:270
+        P2PCHECK(p2p_finalize_mpi(MPI_COMM_WORLD));  // ncclCommDestroy, p2p_matrix.cc:270
     }
 };
 

@@ -21,12 +21,13 @@ CTL_BASE, CTL_STRIDE = 0x100000000000, 0x1000000000
 class OpDesc(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint64) for n in ("local", "nbytes", "seq", "f_wait", "f_signal", "word", "f_wait2",
                                                "f_signal2", "word2", "aux", "arrive")] + \
-               [(n, ctypes.c_uint32) for n in ("kind", "first_block", "nblocks", "peer")]
+               [(n, ctypes.c_uint32) for n in ("kind", "first_block", "nblocks", "peer", "flags", "pad")]
 
 
 class GroupHdr(ctypes.Structure):
-    _fields_ = [(n, ctypes.c_uint32) for n in ("nops", "n_ctrl", "reserved", "tma_chunk", "tma_stages", "pdl")] + \
-               [("timeout_ns", ctypes.c_uint64), ("async_err", ctypes.c_uint64)]
+    _fields_ = [(n, ctypes.c_uint32) for n in ("nops", "n_ctrl", "my_token", "tma_chunk", "tma_stages", "pdl")] + \
+               [("timeout_ns", ctypes.c_uint64), ("async_err", ctypes.c_uint64), ("tokens", ctypes.c_uint64),
+                ("prev_token", ctypes.c_uint32), ("pad", ctypes.c_uint32)]
 
 
 class GroupArgs(ctypes.Structure):
@@ -42,7 +43,8 @@ def owner(addr):
 
 
 def main():
-    spec = json.loads(sys.argv[1])
+    arg = sys.argv[1]
+    spec = json.load(open(arg[1:])) if arg.startswith("@") else json.loads(arg)   # "@file": spec too long for argv
     p2p = importlib.import_module("test-nccl-p2p_b200")
     L = p2p.lib()
     L.p2p_debug_plan_init.argtypes = [ctypes.c_int] * 5
@@ -80,12 +82,13 @@ def main():
         args, grid, block, flavour = GroupArgs(), ctypes.c_uint32(), ctypes.c_uint32(), ctypes.c_int()
         size = L.p2p_debug_plan_last(ctypes.byref(args), ctypes.sizeof(args), ctypes.byref(grid), ctypes.byref(block), ctypes.byref(flavour))
         assert size == ctypes.sizeof(args), (size, ctypes.sizeof(args))
-        rec.update(grid=grid.value, block=block.value, flavour=flavour.value, n_ctrl=args.h.n_ctrl, pdl=args.h.pdl, nops=args.h.nops)
+        rec.update(grid=grid.value, block=block.value, flavour=flavour.value, n_ctrl=args.h.n_ctrl, pdl=args.h.pdl, nops=args.h.nops,
+                   my_token=args.h.my_token, prev_token=args.h.prev_token)
         for i in range(args.h.nops):
             o = args.ops[i]
             rec["ops"].append({
                 "kind": KINDS[o.kind], "local": o.local, "nbytes": o.nbytes, "seq": o.seq, "peer": o.peer,
-                "first_block": o.first_block, "nblocks": o.nblocks, "word": o.word, "word2": o.word2, "aux": o.aux, "arrive": o.arrive,
+                "first_block": o.first_block, "nblocks": o.nblocks, "flags": o.flags, "word": o.word, "word2": o.word2, "aux": o.aux, "arrive": o.arrive,
                 "wait_owner": owner(o.f_wait), "signal_owner": owner(o.f_signal),
                 "wait2_owner": owner(o.f_wait2), "signal2_owner": owner(o.f_signal2),
                 "f_wait": o.f_wait, "f_signal": o.f_signal, "f_wait2": o.f_wait2, "f_signal2": o.f_signal2,

@@ -150,8 +150,7 @@ got = a2a_dst.tensor().cpu().numpy()
 assert np.array_equal(got[: blk * world], oracle.expected_alltoall_recv(blk, 7, rank, world)), rank
 assert np.all(got[blk * world:] == 0xA5)
 torch.cuda.synchronize()
-dist.barrier()
-p2p.finalize()
+p2p.finalize(dist.barrier)
 print("rank ok", rank, flush=True)
 dist.destroy_process_group()
 '''

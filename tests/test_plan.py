@@ -96,8 +96,9 @@ def test_ring_step_pulls_from_the_left_while_the_right_pulls_from_us():
 
 @pytest.mark.parametrize("nranks", [4, 8, 16])
 def test_all_pairs_large_messages(nranks):
-    """Every rank sends 64 MiB to every other and receives as much: pulls with few CTAs per flow
-    (8 GPUs measured: 8 CTAs per flow 4.83 TB/s, pushes 4.28, NCCL 4.6), everything co-resident."""
+    """Every rank sends 64 MiB to every other and receives as much: pulls that share about 64 CTAs between
+    the flows (8 GPUs measured: 8 CTAs per flow 4.83 TB/s, 32 per flow 4.58, pushes 4.28, NCCL 4.6; on 4 GPUs
+    8 per flow starved the three flows: 1.73 vs 2.43 TB/s), never fewer than 8 each, everything co-resident."""
     n, me = 64 * MiB, 1
     group = []
     slot = 0
@@ -108,8 +109,9 @@ def test_all_pairs_large_messages(nranks):
     (g,) = plan(me, nranks, [group])
     ks = kinds(g)
     assert ks.count("post") == nranks - 1 and ks.count("recv_adapt") == nranks - 1 and "push" not in ks
-    assert all(o["nblocks"] == 8 for o in g["ops"] if o["kind"] == "recv_adapt")
-    assert g["n_ctrl"] == nranks - 1 and g["grid"] == 1 + 8 * (nranks - 1) <= 148 * 2
+    per_flow = max(8, 64 // (nranks - 1))
+    assert all(o["nblocks"] == per_flow for o in g["ops"] if o["kind"] == "recv_adapt")
+    assert g["n_ctrl"] == nranks - 1 and g["grid"] == 1 + per_flow * (nranks - 1) <= 148 * 2
     # each pull signals the rank it pulls from; sequence numbers are per peer
     for o in g["ops"]:
         assert o["seq"] == 1
@@ -222,7 +224,8 @@ def test_plan_snapshot():
 
 def test_connect_checks_the_peers_blobs():
     """p2p_connect refuses ranks on another host (NVLink peer mappings stop at the host; the reference
-    tolerates several hosts, p2p_matrix.cc:78-99), ranks with other protocol limits, and blobs out of order."""
+    tolerates several hosts, p2p_matrix.cc:78-99), ranks with other protocol limits, blobs out of order, and
+    two ranks that drive the same GPU."""
     code = r'''
 import ctypes, importlib, struct, sys
 sys.path.insert(0, %r)
@@ -235,9 +238,10 @@ hh, cb = ctypes.c_uint64(), ctypes.c_size_t()
 assert L.p2p_debug_plan_disconnect(ctypes.byref(hh), ctypes.byref(cb)) == 0
 n = L.p2p_blob_bytes()
 
-def blob(rank, host_hash=hh.value, eager=p2p.get_option("eager_bytes"), pull=p2p.get_option("pull_min_bytes"), magic=0x42325032, nranks=2):
-    # BootBlob: magic, version, rank, nranks, host_hash, pid, device, eager_bytes, pull_min_bytes, ctl_bytes, ...
+def blob(rank, host_hash=hh.value, eager=p2p.get_option("eager_bytes"), pull=p2p.get_option("pull_min_bytes"), magic=0x42325032, nranks=2, bus=None):
+    # BootBlob: magic, version, rank, nranks, host_hash, pid, device, eager_bytes, pull_min_bytes, ctl_bytes, pci_bus_id[32], ...
     head = struct.pack("<IIiiQiiQqQ", magic, 1, rank, nranks, host_hash, 424242 + rank, rank, eager, pull, cb.value)
+    head += (bus if bus is not None else ("0000:%%02x:00.0" %% (rank + 1))).encode().ljust(32, b"\0")
     return head + bytes(n - len(head))
 
 def connect(b0, b1):
@@ -256,7 +260,68 @@ rc, why = connect(blob(0), blob(1, magic=7))
 assert rc == p2p.INVALID_ARGUMENT and "not a p2p bootstrap blob" in why, (rc, why)
 rc, why = connect(blob(0), blob(1, nranks=3))
 assert rc == p2p.INVALID_ARGUMENT, (rc, why)
+# two ranks on one GPU: kernels that wait for each other's flags must not share a device
+rc, why = connect(blob(0, bus="0000:1b:00.0"), blob(1, bus="0000:1b:00.0"))
+assert rc == p2p.INVALID_USAGE and "both drive GPU 0000:1b:00.0" in why, (rc, why)
 print("refused as expected")
 ''' % ROOT
     out = run([sys.executable, "-c", code], env={"CUDA_VISIBLE_DEVICES": ""}).stdout
     assert "refused as expected" in out
+
+
+def test_ring_policy_option_makes_the_lone_send_push():
+    """bidir_push 2: a lone large send in a group that also receives a large message from ANOTHER peer (ring
+    step) pushes instead of offering a pull; 1 (pairwise only) keeps offering; 3 extends it to fan-out groups."""
+    n = 256 * MiB
+    ring = [[["recv", RECV_WIN, n, 2], ["send", SEND_WIN, n, 4]]]
+    (g1,) = plan(3, 8, ring, options={"bidir_push": 1})
+    assert kinds(g1) == ["post", "recv_adapt"]
+    (g2,) = plan(3, 8, ring, options={"bidir_push": 2})
+    assert kinds(g2) == ["recv_adapt", "push"]
+    push = g2["ops"][1]
+    assert push["peer"] == 4 and push["nblocks"] == 32 and push["word2"] >> 40 & 0xFF == PUSH_PLEASE
+    assert push["signal2_owner"] == 4 and push["wait_owner"] == 3
+    fan = [[["recv", RECV_WIN, n, 2], ["send", SEND_WIN, n, 4], ["send", SEND_WIN, n, 5]]]
+    (g,) = plan(3, 8, fan, options={"bidir_push": 2})
+    assert kinds(g).count("push") == 0
+    (g,) = plan(3, 8, fan, options={"bidir_push": 3})
+    assert kinds(g).count("push") == 2
+
+
+def test_early_post_only_when_the_launch_ahead_cannot_be_writing_the_payload():
+    """With pdl 3 + early_post a send offered for pulling may be published while the engine launch ahead of it
+    on the same stream is still running - unless that launch receives into the bytes being sent."""
+    n = 16 * MiB
+    groups = [[["send", SEND_WIN, n, 1]],                      # nothing ahead: no early post
+              [["send", SEND_WIN, n, 1]],                      # ahead: a send (writes nothing)
+              [["recv", RECV_WIN, n, 1]],
+              [["send", RECV_WIN + 4096, n, 1]],               # forwards what the launch ahead receives: must wait
+              [["send", SEND_WIN, n, 1]]]
+    res = plan(0, 2, groups, options={"pdl": 3, "early_post": 1})
+    flags = [r["ops"][0]["flags"] for r in res]
+    assert flags == [0, 1, 0, 0, 1]
+    assert [r["pdl"] for r in res] == [3] * 5
+    assert [r["prev_token"] for r in res] == [0] + [r["my_token"] for r in res[:-1]]
+    # off by default
+    res = plan(0, 2, groups)
+    assert all(r["ops"][0]["flags"] == 0 for r in res) and all(r["pdl"] == 0 for r in res)
+
+
+def test_options_from_the_environment_are_range_checked():
+    """The same checks as p2p_set_option: a bad P2P_* value fails p2p_init instead of dividing by zero later."""
+    code = r'''
+import ctypes, importlib, sys
+sys.path.insert(0, %r)
+p2p = importlib.import_module("test-nccl-p2p_b200")
+L = p2p.lib()
+L.p2p_debug_plan_init.argtypes = [ctypes.c_int] * 5
+rc = L.p2p_debug_plan_init(0, 2, 148, 2, 1)
+print("rc", rc, L.p2p_get_last_error().decode())
+''' % ROOT
+    for env, word in (({"P2P_TMA_CHUNK": "0"}, "tma_chunk"), ({"P2P_TMA_STAGES": "0"}, "tma_stages"),
+                      ({"P2P_TMA_CHUNK": "4100"}, "multiple of 16"), ({"P2P_TMA_CHUNK": "65536", "P2P_TMA_STAGES": "8"}, "200 KiB"),
+                      ({"P2P_NBLOCKS": "-3"}, "nblocks"), ({"P2P_TIMEOUT_MS": "-1"}, "timeout_ms"), ({"P2P_EAGER_BYTES": "2000000"}, "eager_bytes")):
+        out = run([sys.executable, "-c", code], env={"CUDA_VISIBLE_DEVICES": "", **env}).stdout
+        assert out.startswith("rc 4 ") and word in out, (env, out)
+    out = run([sys.executable, "-c", code], env={"CUDA_VISIBLE_DEVICES": "", "P2P_TMA_CHUNK": "16384", "P2P_PATH": "tma"}).stdout
+    assert out.startswith("rc 0"), out

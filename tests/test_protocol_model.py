@@ -19,6 +19,7 @@ import json
 import os
 import random
 import sys
+import tempfile
 
 import pytest
 
@@ -29,6 +30,7 @@ SEND_WIN, RECV_WIN = 1 << 32, 1 << 33
 WINDOWS = [[SEND_WIN, 1 << 30], [RECV_WIN, 4 << 30]]
 VALID, OFFMASK, PUSH_PLEASE = 1 << 39, (1 << 39) - 1, 0xFF
 MiB = 1 << 20
+CLEAR_CONSUMED_SLOTS = True   # what the device code does; the wrap test below also shows what happens without
 
 
 def plans_for(nranks, programs, options=None):
@@ -36,7 +38,16 @@ def plans_for(nranks, programs, options=None):
     out = []
     for r in range(nranks):
         spec = {"rank": r, "nranks": nranks, "groups": programs[r], "windows": WINDOWS, "options": options or {}}
-        res = run([sys.executable, PROBE, json.dumps(spec)], env={"CUDA_VISIBLE_DEVICES": ""}).stdout
+        text = json.dumps(spec)
+        if len(text) > 100_000:
+            with tempfile.NamedTemporaryFile("w", suffix=".json", delete=False) as tf:
+                tf.write(text)
+            try:
+                res = run([sys.executable, PROBE, "@" + tf.name], env={"CUDA_VISIBLE_DEVICES": ""}, timeout=900).stdout
+            finally:
+                os.unlink(tf.name)
+        else:
+            res = run([sys.executable, PROBE, text], env={"CUDA_VISIBLE_DEVICES": ""}).stdout
         groups = json.loads(res.strip().splitlines()[-1])
         assert all(g["rc"] == 0 for g in groups), groups
         out.append(groups)
@@ -74,6 +85,8 @@ def role(world, rank, op):
             yield
         dst = window_local(world.tagged(op["f_wait"], seq))
         world.mem[peer][dst] = ("payload", rank, op["local"], op["nbytes"])
+        if CLEAR_CONSUMED_SLOTS:
+            world.flags[op["f_wait"]] = 0      # movers_signal: the last CTA zeroes the slot the post arrived in
         world.flags[op["f_signal"]] = seq
     elif k == "recv_adapt":
         while world.tagged(op["f_wait2"], seq) is None:
@@ -84,8 +97,12 @@ def role(world, rank, op):
             world.flags[op["f_signal"]] = op["word"]
             while world.flags.get(op["f_wait"], 0) != seq:
                 yield
+            if CLEAR_CONSUMED_SLOTS:
+                world.flags[op["f_wait2"]] = 0
         else:
             world.mem[rank][op["local"]] = ("payload", peer, window_local(word), op["nbytes"])
+            if CLEAR_CONSUMED_SLOTS:
+                world.flags[op["f_wait2"]] = 0
             world.flags[op["f_signal2"]] = seq
     elif k == "send_ll":
         if seq > 4:
@@ -218,3 +235,20 @@ def test_unregistered_send_buffers_fall_back_to_push():
         check_phases(3, [[(0, 1, 8 * MiB), (1, 2, 8 * MiB), (2, 0, 8 * MiB)], [(0, 2, 32 * MiB)]], seeds=(3,))
     finally:
         SEND_WIN = keep
+
+
+def test_sequence_tag_wraps_after_65536_messages():
+    """Post words carry a 16-bit sequence tag.  Message 1 is pushed (its post lands in slot 1 of the sender's
+    post ring), the next 65535 are pulled (they use the other ring and never rewrite that slot), message 65537
+    is pushed again into ANOTHER buffer: its tag and slot equal message 1's.  The consumer zeroes a slot once
+    the word in it has been used, so the old post cannot be taken for the new one; without that the payload
+    goes to message 1's address whenever the sender runs before the receiver has posted."""
+    global CLEAR_CONSUMED_SLOTS
+    phases = [[(0, 1, 2 * MiB)]] + [[(0, 1, 8 * MiB)]] * 65535 + [[(0, 1, 8), (0, 1, 2 * MiB)]]
+    check_phases(2, phases, seeds=(1, 2, 3, 4))
+    CLEAR_CONSUMED_SLOTS = False
+    try:
+        with pytest.raises(AssertionError):
+            check_phases(2, phases, seeds=(1, 2, 3, 4))
+    finally:
+        CLEAR_CONSUMED_SLOTS = True
