@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--size", type=int, default=256 << 20)
+    ap.add_argument("--no-parity", action="store_true", help="skip the engine-vs-NCCL digest comparison at N >= 2")
     ap.add_argument("--no-extras", action="store_true", help="skip the side measurements (latency, all-pairs, NCCL in the same run, CPU baseline); used for profiling runs")
     return ap.parse_args()
 
@@ -159,6 +160,58 @@ def nccl_run(n: int, mode: str, size: int, iters: int, warmup: int, extra=(), ti
         return None, "oracle/_ref/p2p_matrix_nccl not built"
     return run_json([MPIRUN, "-n", str(n), exe, "--mode", mode, "--size", str(size), "--iters", str(iters), "--warmup", str(warmup),
                      "--timing", "dev", *extra], timeout)
+
+
+def matrix_run(exe, n: int, args, timeout=900):
+    """One run of ./p2p_matrix or of the NCCL harness (same driver, same flags) under the MPI launcher."""
+    if not (os.path.exists(exe) and os.path.exists(MPIRUN)):
+        return None, f"{exe} or {MPIRUN} not built"
+    return run_json([MPIRUN, "-n", str(n), exe, *args], timeout)
+
+
+def nccl_parity(n: int, size: int):
+    """Cross-GPU parity against the reference's library, on this box, in this run: the engine (./p2p_matrix) and
+    the reference's ncclSend/ncclRecv loop (oracle/_ref/p2p_matrix_nccl) move the same patterned payloads — the
+    ring step at the bench's message size, then every cell of the reference's uni- and bi-directional matrices
+    (p2p_matrix.cc:141-186, :196-267) at an odd size — and the digests of what every receiver holds must agree.
+    NCCL's buffers are copied to the host and digested by the CPU oracle (oracle/pattern.c); the engine's are
+    digested on the device by a kernel that the tests pin to that same oracle."""
+    engine_exe, nccl_exe = os.path.join(ROOT, "p2p_matrix"), os.path.join(REF_DIR, "p2p_matrix_nccl")
+    legs = [("ring", ["--mode", "ring", "--size", str(size), "--iters", "1", "--warmup", "0", "--timing", "dev", "--verify", "--seed", "0x5EED0002"]),
+            ("matrices", ["--mode", "ref", "--size", "5000011", "--iters", "1", "--verify", "--seed", "0x5EED0003"])]
+    out = {"nccl_digests_equal": True, "cells": 0, "mismatching_bytes": 0, "what": nccl_parity.__doc__.split(":")[0].strip()}
+    for name, args in legs:
+        sets = {}
+        for who, exe in (("engine", engine_exe), ("nccl", nccl_exe)):
+            recs, log = matrix_run(exe, n, args)
+            if recs is None:
+                return {"nccl_digests_equal": None, "unavailable": f"{who} {name}: {str(log)[-300:]}"}
+            sets[who] = {(r["dir"], r["src"], r["dst"], r["bytes"]): (r["digest"], r["mismatches"]) for r in recs if r["mode"] == "verify"}
+        e, c = sets["engine"], sets["nccl"]
+        equal = bool(e) and e == c
+        out[name] = {"cells": len(e), "equal": equal}
+        out["cells"] += len(e)
+        out["mismatching_bytes"] += sum(bad for _, bad in e.values()) + sum(bad for _, bad in c.values())
+        if not equal:
+            out["nccl_digests_equal"] = False
+            diff = [k for k in set(e) | set(c) if e.get(k) != c.get(k)]
+            out[name]["first_difference"] = [list(diff[0]), e.get(diff[0]), c.get(diff[0])] if diff else "one side is empty"
+    if out["mismatching_bytes"]:
+        out["nccl_digests_equal"] = False
+    return out
+
+
+def nccl_side_numbers(n: int, allpairs_bytes: int):
+    """The NCCL figures the north star compares with, taken in the same run: all-pairs aggregate, 8-byte latency."""
+    out = {}
+    exe = os.path.join(REF_DIR, "p2p_matrix_nccl")
+    recs, log = matrix_run(exe, n, ["--mode", "allpairs", "--size", str(allpairs_bytes), "--iters", "30", "--warmup", "3", "--timing", "dev"])
+    ap = [r for r in (recs or []) if r["mode"] == "allpairs"]
+    out["nccl_allpairs_aggregate_GBps"] = round(ap[0]["GBps"], 2) if ap else None
+    recs, log = matrix_run(exe, n, ["--mode", "latency", "--sweep-min", "8", "--sweep-max", "8", "--iters", "2000"])
+    lat = [r for r in (recs or []) if r["mode"] == "latency" and r["bytes"] == 8]
+    out["nccl_latency_8B_oneway_us"] = round(lat[0]["us"], 3) if lat else None
+    return out
 
 
 # ------------------------------------------------------------------ the reference arm
@@ -281,7 +334,6 @@ def engine_arm(args):
         return max_over_ranks(e0.elapsed_time(e1) * 1e-3)
 
     digest_before = verify(1)
-    plan = p2p.query_plan(B, right)
     for _ in range(W):
         step()
     stream.synchronize()
@@ -289,6 +341,8 @@ def engine_arm(args):
     total = timed(step, K)
     launches = p2p.get_option("stat_launches") - launches0      # kernels the engine launched in the timed region
     ce_copies = p2p.get_option("stat_ce_copies") - ce0          # payloads it handed to the copy engine instead
+    last = {k: p2p.get_option("stat_last_" + k) for k in ("flavour", "grid", "block", "push_ops", "push_ctas", "offer_ops", "recv_ops",
+                                                          "recv_ctas", "copy_ctas", "ce_ops", "pdl")}   # the group the timed loop launched
     p2p.raise_async_error()
     digest_after = verify(2)
     per_step = total / K
@@ -318,7 +372,7 @@ def engine_arm(args):
     # ---- side measurements the north star asks to sit next to the number (not part of `value`)
     extras = {}
     if not args.no_extras:
-        extras = side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks)
+        extras = side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks, gather)
 
     peaks, peak_kind = measured_peaks()
     if world == 1:
@@ -329,16 +383,30 @@ def engine_arm(args):
                 "peak_kind": f"nominal NVLink 5 per direction per GPU; measured peer copy on this pool {LINK_MEASURED_GBPS}",
                 "traffic": TRAFFIC_PER_LAUNCH.get("peer")}
     roof["frac"] = round(roof["achieved"] / roof["peak"], 4)
-    roof["kernel"] = "p2p_group_kernel_tma" if plan[0] == p2p.PATH_TMA else "p2p_group_kernel_ldst"
+    if world > 1:
+        roof["frac_measured"] = round(roof["achieved"] / LINK_MEASURED_GBPS, 4)
+        roof["peak_measured"] = LINK_MEASURED_GBPS
+    roof["kernel"] = "p2p_group_kernel_tma" if last["flavour"] == 2 else "p2p_group_kernel_ldst"
+    if world == 1:
+        how = f"local copy, {'TMA ring' if last['flavour'] == 2 else 'ld/st'}, {last['copy_ctas']} CTAs"
+    else:
+        # this rank's view of the group it launched: how its send leaves, how its receive is served
+        send = (f"send pushed by {last['push_ctas']} CTAs (ld/st stores into the peer's buffer)" if last["push_ops"] else
+                "send handed to the copy engine" if last["ce_ops"] else
+                "send offered for pulling (the receiver's CTAs load it)" if last["offer_ops"] else "no send")
+        recv = f"receive served by {last['recv_ctas']} CTAs (pull, or post-and-wait when the sender pushes)" if last["recv_ops"] else "no receive"
+        how = f"{send}; {recv}"
     if ce_copies:
-        roof["kernel"] = (f"copy engine (cudaMemcpyAsync to the peer mapping) for {ce_copies} of {K} payloads of this rank, "
-                          "between ce_wait_kernel / ce_signal_kernel; receives in p2p_group_kernel_ldst")
+        roof["kernel"] = (f"copy engine (cudaMemcpyAsync to the peer mapping) for {ce_copies} of {K} payloads of this rank; "
+                          "receives in p2p_group_kernel_ldst")
     roof["algorithmic_bytes_per_launch"] = (2 if world == 1 else 1) * B
-    roof["ctas"] = plan[1]
+    roof["ctas"] = last["grid"]
+    roof["threads_per_cta"] = last["block"]
 
     torch.cuda.synchronize()
     p2p.finalize((lambda: dist.barrier(group=host_group)) if world > 1 else None)
 
+    parity_failed = False
     if rank == 0:
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -347,8 +415,7 @@ def engine_arm(args):
             "config": {"workload": f"ring step, {B} bytes per GPU (BASELINE configs[1] message size)"
                                    + ("; N=1: local HBM copy through the same send/recv kernel" if world == 1 else ""),
                        "bytes": B, "l2": "message larger than L2 (126 MB), no flush needed" if B > (126 << 20) else "message fits L2",
-                       "path": ("local copy, " if world == 1 else "") + {1: "push ld/st", 2: "push tma", 4: "eager", 5: "pull ld/st"}.get(plan[0], str(plan[0])),
-                       "ctas": plan[1]},
+                       "path": how, "ctas": last["grid"], "pdl": last["pdl"]},
             "clocks": clocks.summary(),
             "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": B * world, "d2h_bytes_per_step": B * world,
                     "steps": e2e_steps, "payload_intact": e2e_ok},
@@ -360,6 +427,11 @@ def engine_arm(args):
             line["cpu_baseline"] = cpu_baseline(B)
         if extras:
             line["extras"] = extras
+        if world > 1 and not args.no_parity:
+            line["parity"].update(nccl_parity(world, B))
+            parity_failed = line["parity"].get("nccl_digests_equal") is False
+        if world > 1 and not args.no_extras:
+            line["extras"].update(nccl_side_numbers(world, extras.get("allpairs_bytes_per_flow", 64 << 20)))
         if not args.no_extras:
             recs, log = nccl_run(world, "ring", B, min(K, 200), 5)
             ring = [r for r in (recs or []) if r["mode"] == "ring"]
@@ -370,6 +442,9 @@ def engine_arm(args):
     if world > 1:
         dist.barrier(group=host_group)
         dist.destroy_process_group()
+    if parity_failed:
+        sys.stderr.write("bench.py: the engine's received bytes differ from NCCL's for the same payloads (see the line's parity key)\n")
+        return 3
     return 0
 
 
@@ -379,7 +454,7 @@ def engine_arm(args):
 TRAFFIC_PER_LAUNCH = {"local": 481247232, "peer": None}
 
 
-def side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks):
+def side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks, gather):
     """8-byte one-way latency, single-pair uni/bidir bandwidth and all-pairs aggregate (N >= 2)."""
     out = {}
     if world < 2:
@@ -436,15 +511,17 @@ def side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max
         out[f"bidir_0and1_{name}_GBps"] = round(2 * n / (t / 50) / 1e9, 2)
 
     # all-pairs: every rank sends 64 MiB to each of the other ranks at once (BASELINE configs[3])
-    n = min(64 << 20, B // max(world - 1, 1))
-    n -= n % 256
+    n = min(64 << 20, B)
+    slots = p2p.DeviceBuffer((world - 1) * n)      # one receive slot per peer, as the reference's buffers would need
+    p2p.register(slots.ptr, slots.nbytes, gather)
+
     def allpairs():
         with p2p.group():
             slot = 0
             for p in range(world):
                 if p == rank:
                     continue
-                p2p.recv(dst.ptr + slot * n, n, p2p.INT8, p, stream)
+                p2p.recv(slots.ptr + slot * n, n, p2p.INT8, p, stream)
                 slot += 1
             for p in range(world):
                 if p != rank:

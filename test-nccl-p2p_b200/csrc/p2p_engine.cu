@@ -128,6 +128,9 @@ struct Options {
                                    // it loses to the pull kernel (256 MiB: 708 vs 726 GB/s streamed, 496 vs 368 us per
                                    // ping-pong hop): kernel -> DMA -> kernel on one stream costs more than the DMA gains.
     long long ce_wait_us = 200;    // how long p2p_send's host side waits for that word before using the SM path
+    long long ce_flags = 1;        // who handles the flags around the DMA: 0 two one-thread kernels (round 1), 1 stream memory
+                                   // operations (cuStreamWaitValue64 / cuStreamWriteValue64: nothing to launch, so the chain
+                                   // may run beside a group's kernel), 2 as 1 but flags in PEER memory are written by 8-byte DMA
 };
 
 struct Engine {
@@ -165,6 +168,8 @@ struct Engine {
     cudaEvent_t ce_join[P2P_MAX_RANKS] = {};
     cudaEvent_t ce_fork = nullptr;
     long long stat_launches = 0, stat_ce_copies = 0;
+    uint64_t* ce_vals = nullptr;                // pinned host ring of flag values for ce_flags 2 (source of the 8-byte DMAs)
+    uint32_t ce_vals_next = 0;
     // what the last launched group looked like (bench.py reports the kernel that actually ran, not a forecast)
     long long last_stat[12] = {};
     uint32_t* tokens = nullptr;                 // device u32[kTokenSlots], see publish_token()
@@ -290,6 +295,7 @@ const OptionSpec kOptionSpecs[] = {
     {"fan_min", "P2P_FAN_MIN", &Options::fan_min, 1, 64},
     {"ce_min_bytes", "P2P_CE_MIN_BYTES", &Options::ce_min_bytes, -1, 1ll << 40},
     {"ce_wait_us", "P2P_CE_WAIT_US", &Options::ce_wait_us, 0, 10000000},
+    {"ce_flags", "P2P_CE_FLAGS", &Options::ce_flags, 0, 2},
 };
 
 const OptionSpec* find_option(const char* name) {
@@ -347,7 +353,9 @@ bool hostbox_lookup(int dst, uint64_t seq, long long wait_us, uint64_t* word) {
     HostPost* e = hostbox_entry(dst, g.rank, seq);
     const auto t0 = std::chrono::steady_clock::now();
     for (;;) {
-        if (e->seq.load(std::memory_order_acquire) == seq) {
+        const uint64_t have = e->seq.load(std::memory_order_acquire);
+        if (have > seq) return false;  // the receiver's host is more than a ring ahead: the entry is gone
+        if (have == seq) {
             const uint64_t w = e->word.load(std::memory_order_relaxed);
             std::atomic_thread_fence(std::memory_order_acquire);
             if (e->seq.load(std::memory_order_relaxed) == seq) {
@@ -589,6 +597,8 @@ void assign_sequence(const std::vector<PendingOp>& ops, std::vector<Resolved>& r
     }
 }
 
+bool memops_ready();
+
 // Copy engine (opt-in) for a send that is alone in its group and whose destination the host already knows.
 // Alone, because the chain runs beside the group's kernel on another stream and a receive in that kernel may
 // depend on it: two launches that must overlap are not something a GPU promises.  Never waits longer than
@@ -598,7 +608,9 @@ void choose_copy_engine(const std::vector<PendingOp>& ops, std::vector<Resolved>
         Resolved& r = res[i];
         const PendingOp& op = ops[i];
         if (!(op.is_send && r.proto == PROTO_LARGE && op.peer != g.rank)) continue;
-        if (g.opt.ce_min_bytes < 0 || (long long)op.nbytes < g.opt.ce_min_bytes || ops.size() != 1) continue;
+        if (g.opt.ce_min_bytes < 0 || (long long)op.nbytes < g.opt.ce_min_bytes) continue;
+        if (g.opt.ce_flags == 0 && ops.size() != 1) continue;  // a chain with kernels in it must not have to overlap the group's
+        if (g.opt.ce_flags != 0 && !memops_ready()) continue;
         if (g.opt.path != 0 && g.opt.path != 3) continue;
         uint64_t word = 0;
         if (!hostbox_lookup(op.peer, r.seq, g.opt.ce_wait_us, &word) || word == 0) continue;
@@ -796,7 +808,46 @@ uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolve
     return next_block;
 }
 
-// One copy-engine chain: ce_wait (announce the push, wait for the receiver's post) -> DMA -> ce_signal.
+// Stream memory operations of the driver API (the runtime API has no equivalent), resolved once.
+typedef int (*cuStreamMemOp64_t)(cudaStream_t stream, unsigned long long addr, unsigned long long value, unsigned int flags);
+struct MemOps {
+    cuStreamMemOp64_t wait = nullptr, write = nullptr;
+    int state = 0;  // 0 not tried, 1 usable, -1 unavailable
+};
+MemOps g_memops;
+constexpr unsigned kWaitValueEq = 1;  // CU_STREAM_WAIT_VALUE_EQ
+
+bool memops_ready() {
+    if (g_memops.state) return g_memops.state > 0;
+    g_memops.state = -1;
+    void *w = nullptr, *x = nullptr;
+    cudaDriverEntryPointQueryResult q1, q2;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue64", &w, cudaEnableDefault, &q1) != cudaSuccess || q1 != cudaDriverEntryPointSuccess || !w)
+        return false;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue64", &x, cudaEnableDefault, &q2) != cudaSuccess || q2 != cudaDriverEntryPointSuccess || !x)
+        return false;
+    g_memops.wait = (cuStreamMemOp64_t)w;
+    g_memops.write = (cuStreamMemOp64_t)x;
+    g_memops.state = 1;
+    return true;
+}
+
+// 8 bytes into a flag, in stream order, without a kernel: a stream memory operation, or (ce_flags 2, for flags in
+// peer memory) a DMA from a pinned ring of values.
+int stream_write_flag(cudaStream_t cs, uint64_t* flag, uint64_t value, bool in_peer_memory) {
+    if (g.opt.ce_flags == 2 && in_peer_memory) {
+        uint64_t* src = g.ce_vals + (g.ce_vals_next++ % 4096);
+        *src = value;
+        CUDA_TRY(cudaMemcpyAsync(flag, src, sizeof(uint64_t), cudaMemcpyDefault, cs));
+        return P2P_SUCCESS;
+    }
+    const int r = g_memops.write(cs, (unsigned long long)flag, value, 0);
+    if (r != 0) return fail(P2P_UNHANDLED_CUDA_ERROR, "cuStreamWriteValue64 on %s memory failed with CUresult %d", in_peer_memory ? "peer" : "local", r);
+    return P2P_SUCCESS;
+}
+
+// One copy-engine chain on a side stream: tell the receiver "I will push", wait for its post (buffer ready),
+// DMA the payload into the peer mapping, publish completion.  Readiness and completion stay on the device.
 int submit_copy_engine_chain(const PendingOp& op, const Resolved& r, const GroupHdr& hdr, cudaStream_t launch_stream) {
     const int me = g.rank, p = op.peer;
     const uint64_t seq = r.seq, word = r.ce_word;
@@ -806,15 +857,30 @@ int submit_copy_engine_chain(const PendingOp& op, const Resolved& r, const Group
     }
     uint8_t* theirs = g.peer_ctl[p];
     uint8_t* dst = g.windows[(word >> 40) & 0xffu].peer_base[p] + (word & kPostOffMask);
+    uint64_t* notice = &peer_section(theirs, me)->pull_post[seq % kRing];
+    uint64_t* post = &peer_section(g.ctl, p)->post[seq % kRing];
+    uint64_t* done = &peer_section(theirs, me)->done[seq % kRing];
     cudaStream_t cs = g.ce_stream[p];
     CUDA_TRY(cudaStreamWaitEvent(cs, g.ce_fork, 0));
-    CUDA_TRY(launch_ce_wait(&peer_section(theirs, me)->pull_post[seq % kRing], make_post_word(seq, kWinPushPlease, 0),
-                            &peer_section(g.ctl, p)->post[seq % kRing], seq, word, hdr, cs));
-    CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
-    CUDA_TRY(launch_ce_signal(&peer_section(theirs, me)->done[seq % kRing], seq, cs));
+    if (g.opt.ce_flags == 0) {
+        CUDA_TRY(launch_ce_wait(notice, make_post_word(seq, kWinPushPlease, 0), post, seq, word, hdr, cs));
+        CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
+        CUDA_TRY(launch_ce_signal(done, seq, cs));
+        g.stat_launches += 2;
+    } else {
+        int rc = stream_write_flag(cs, notice, make_post_word(seq, kWinPushPlease, 0), true);
+        if (rc) return rc;
+        // the host was told the very word the device will post (choose_copy_engine): wait for exactly that
+        const int wr = g_memops.wait(cs, (unsigned long long)post, word, kWaitValueEq);
+        if (wr != 0) return fail(P2P_UNHANDLED_CUDA_ERROR, "cuStreamWaitValue64 failed with CUresult %d", wr);
+        rc = stream_write_flag(cs, post, 0, false);  // consumed (see movers_signal)
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
+        rc = stream_write_flag(cs, done, seq, true);
+        if (rc) return rc;
+    }
     CUDA_TRY(cudaEventRecord(g.ce_join[p], cs));
     CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ce_join[p], 0));
-    g.stat_launches += 2;
     g.stat_ce_copies++;
     return P2P_SUCCESS;
 }
@@ -1057,6 +1123,8 @@ int p2p_init(int rank, int nranks, int device) {
         g.hostbox_name[0] = '\0';
     }
     CUDA_TRY(cudaEventCreateWithFlags(&g.ce_fork, cudaEventDisableTiming));
+    CUDA_TRY(cudaHostAlloc(&g.ce_vals, sizeof(uint64_t) * 4096, cudaHostAllocDefault));
+    g.ce_vals_next = 0;
     g.stat_launches = g.stat_ce_copies = 0;
     g.inited = true;
     g.connected = false;
@@ -1214,6 +1282,8 @@ int p2p_finalize(void) {
     }
     if (g.ce_fork) cudaEventDestroy(g.ce_fork);
     g.ce_fork = nullptr;
+    if (g.ce_vals) cudaFreeHost(g.ce_vals);
+    g.ce_vals = nullptr;
     cudaFree(g.ctl);
     cudaFree(g.arrive);
     cudaFree(g.win_table);

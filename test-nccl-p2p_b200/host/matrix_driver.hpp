@@ -521,9 +521,20 @@ public:
             o_.e2e = false;
             step(true);
             o_.e2e = keep;
-            uint64_t digest;
+            uint64_t digest = 0;
             unsigned long long b = be_.check(recv_, bytes, o_.seed, left, 4242, s0_, &digest), total = 0;
             MPICHECK(MPI_Allreduce(&b, &total, 1, MPI_UINT64_T, MPI_SUM, MPI_COMM_WORLD));
+            // one record per receiver: what it holds after the step (compared across backends by bench.py)
+            std::vector<unsigned long long> digs((size_t)size_), bads((size_t)size_);
+            unsigned long long dg = digest;
+            MPICHECK(MPI_Allgather(&dg, 1, MPI_UINT64_T, digs.data(), 1, MPI_UINT64_T, MPI_COMM_WORLD));
+            MPICHECK(MPI_Allgather(&b, 1, MPI_UINT64_T, bads.data(), 1, MPI_UINT64_T, MPI_COMM_WORLD));
+            if (json_)
+                for (int r = 0; r < size_; ++r)
+                    fprintf(json_,
+                            "{\"backend\": \"%s\", \"mode\": \"verify\", \"dir\": \"ring\", \"ranks\": %d, \"src\": %d, \"dst\": %d, "
+                            "\"bytes\": %zu, \"seed\": %llu, \"iter\": 4242, \"mismatches\": %llu, \"digest\": \"0x%016llx\"}\n",
+                            be_.name(), size_, (r + size_ - 1) % size_, r, bytes, (unsigned long long)o_.seed, bads[(size_t)r], digs[(size_t)r]);
             verified_cells_ += (uint64_t)size_;
             verified_bytes_ += (uint64_t)size_ * bytes;
             verify_failures_ += total;

@@ -26,11 +26,19 @@ def matrix(n, *args, env=None, timeout=600):
     return run([MPIRUN, "-n", str(n), P2P_MATRIX, *args], timeout=timeout, env=env).stdout
 
 
-@pytest.mark.parametrize("path", ["auto", "ldst", "tma", "ce"])
+@pytest.mark.parametrize("path", ["auto", "ldst", "tma", "ce_kernels", "ce_memops", "ce_dma", "pdl3_early", "ring_push"])
 @pytest.mark.parametrize("n", RANKS)
 def test_reference_loops_verified(built, n, path):
-    # "ce": opt in to the copy-engine path for the one-way loop (a send alone in its group); off by default
-    env = {"P2P_PATH": "auto", "P2P_CE_MIN_BYTES": "4194304", "P2P_CE_WAIT_US": "20000"} if path == "ce" else {"P2P_PATH": path}
+    # "ce_*": opt in to the copy-engine path (off by default), flags handled by kernels / stream memory operations / 8-byte DMAs
+    if path.startswith("ce_"):
+        env = {"P2P_PATH": "auto", "P2P_CE_MIN_BYTES": "4194304", "P2P_CE_WAIT_US": "20000",
+               "P2P_CE_FLAGS": {"ce_kernels": "0", "ce_memops": "1", "ce_dma": "2"}[path]}
+    elif path == "pdl3_early":
+        env = {"P2P_PDL": "3", "P2P_EARLY_POST": "1"}
+    elif path == "ring_push":
+        env = {"P2P_BIDIR_PUSH": "2"}
+    else:
+        env = {"P2P_PATH": path}
     out = matrix(n, "--size", "8M", "--iters", "4", "--verify", env=env)
     assert "verify: OK" in out and "VERIFY FAILED" not in out
     assert "Evaluating the Uni-Directional NCCL P2P Bandwidth (Gbps)" in out
@@ -49,11 +57,14 @@ def test_large_message_with_unregistered_send_buffer(built):
     assert "verify: OK" in out and "VERIFY FAILED" not in out
 
 
-def test_allpairs_and_ring_verified(built):
+@pytest.mark.parametrize("env", [{}, {"P2P_BIDIR_PUSH": "2"}, {"P2P_BIDIR_PUSH": "3"}, {"P2P_PDL": "3", "P2P_EARLY_POST": "1"},
+                                 {"P2P_CE_MIN_BYTES": "4194304", "P2P_CE_WAIT_US": "20000"}],
+                         ids=["default", "ring_push", "always_push", "pdl3_early", "copy_engine"])
+def test_allpairs_and_ring_verified(built, env):
     n = RANKS[-1]
     for mode in ("allpairs", "ring"):
         for size in ("4096", "16M"):
-            out = matrix(n, "--mode", mode, "--size", size, "--iters", "3", "--warmup", "1", "--timing", "dev", "--verify")
+            out = matrix(n, "--mode", mode, "--size", size, "--iters", "3", "--warmup", "1", "--timing", "dev", "--verify", env=env)
             assert "verify: OK" in out, out
 
 

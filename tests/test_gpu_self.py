@@ -109,6 +109,46 @@ def test_pull_path(eng, n, src_off, dst_off):
         eng.p2p.set_option("bidir_push", 1)
 
 
+@pytest.mark.parametrize("pdl,early", [(2, 0), (3, 0), (3, 1)])
+@pytest.mark.parametrize("bidir_push", [0, 1])
+def test_pdl_modes_back_to_back(eng, pdl, early, bidir_push):
+    """Programmatic dependent launch for every group (trigger at kernel entry, or after the copy loop), with and
+    without early posts: six messages of every protocol enqueued back to back on one stream, no host sync in
+    between, each into its own part of the receive buffer; every byte compared afterwards."""
+    p2p, torch = eng.p2p, eng.torch
+    p2p.set_option("path", p2p.PATH_AUTO)
+    p2p.set_option("pdl", pdl)
+    p2p.set_option("early_post", early)
+    p2p.set_option("bidir_push", bidir_push)
+    sizes = [(8 << 20) + 16, 2 << 20, 1000, (5 << 20) + 3, 8, 6 << 20]
+    try:
+        for rep in range(2):
+            offs, off = [], 0
+            for n in sizes:
+                offs.append(off)
+                off += (n + 4095) // 4096 * 4096 + 4096
+            base_it = 1000 + 10 * rep + 100 * pdl + early
+            for k, n in enumerate(sizes):
+                p2p.pattern_fill(eng.src.ptr + offs[k], n, SEED, 0, base_it + k, eng.stream)
+            eng.dst.tensor().fill_(0xA5)
+            torch.cuda.synchronize()
+            for k, n in enumerate(sizes):
+                with p2p.group():
+                    p2p.recv(eng.dst.ptr + offs[k], n, p2p.INT8, 0, eng.stream)
+                    p2p.send(eng.src.ptr + offs[k], n, p2p.INT8, 0, eng.stream)
+            eng.stream.synchronize()
+            p2p.raise_async_error()
+            got = eng.dst.tensor()[:off].cpu().numpy()
+            for k, n in enumerate(sizes):
+                want = eng.oracle.expected_recv(n, SEED, 0, base_it + k)
+                assert np.array_equal(got[offs[k]: offs[k] + n], want), (pdl, early, k, n)
+                assert np.all(got[offs[k] + n: offs[k] + n + 64] == 0xA5), "wrote past the end of a message"
+    finally:
+        p2p.set_option("pdl", 1)
+        p2p.set_option("early_post", 0)
+        p2p.set_option("bidir_push", 1)
+
+
 def test_large_message_fallbacks(eng):
     """Large message with only one side registered: unregistered sender -> it announces a push;
     unregistered receiver -> pull still works; neither -> reported, not hung."""

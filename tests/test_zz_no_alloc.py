@@ -72,6 +72,25 @@ def test_edges_and_limit(engine):
     assert L.p2p_digest_noalloc(ctypes.c_void_p(buf.data_ptr()), 16, None, None) == p2p.INVALID_ARGUMENT
 
 
+def test_exactly_the_largest_buffer_the_scratch_covers(engine):
+    """bytes == P2P_NOALLOC_MAX_BYTES: all 4096 partial-sum slots in use (the last CTA covers the last 256 KiB),
+    and one byte less (the last slot only partly filled); both must match the allocating digest."""
+    p2p, torch = engine
+    n = p2p.NOALLOC_MAX_BYTES
+    stream = torch.cuda.Stream()
+    buf = torch.empty(n, dtype=torch.uint8, device="cuda")
+    out = torch.zeros(2, dtype=torch.int64, device="cuda")
+    p2p.pattern_fill(buf.data_ptr(), n, 77, 1, 5, stream)
+    p2p.digest_noalloc(buf.data_ptr(), n, out.data_ptr(), stream)
+    p2p.digest_noalloc(buf.data_ptr(), n - 1, out.data_ptr() + 8, stream)
+    stream.synchronize()
+    got = out.cpu().numpy().view(np.uint64)
+    assert int(got[0]) == p2p.digest(buf.data_ptr(), n, stream)
+    assert int(got[1]) == p2p.digest(buf.data_ptr(), n - 1, stream)
+    assert int(got[0]) != int(got[1])
+    del buf
+
+
 def test_works_in_a_process_that_never_initialised_the_engine(p2p, oracle):
     """Fresh process, no p2p_init, no allocation by the library: the value still matches."""
     from conftest import ROOT, run
