@@ -93,7 +93,7 @@ typedef enum {
 } p2p_datatype_t;
 
 #define P2P_MAX_RANKS 16      /* one NVSwitch domain on one host */
-#define P2P_MAX_WINDOWS 255   /* registered windows per rank */
+#define P2P_MAX_WINDOWS 254   /* registered windows per rank (ids 254 and 255 are protocol words) */
 #define P2P_MAX_GROUP_OPS 32  /* sends + recvs in one group */
 
 /* ---- lifecycle: replaces ncclGetUniqueId + MPI_Bcast + ncclCommInitRank

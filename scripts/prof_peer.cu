@@ -75,7 +75,7 @@ int main(int argc, char** argv) {
     }
 
     cudaEvent_t e0, e1;
-    CK(cudaSetDevice(dev));
+    CK(cudaSetDevice(!strcmp(mode, "ll") ? 1 : dev));  // events live on the device whose stream records them
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     float ms = 0;
     if (strcmp(mode, "ll")) {

@@ -38,10 +38,12 @@ enum OpKind : uint32_t {
     OP_RECV_LL = 4,
     OP_COPY = 5,        // mover CTAs: local -> local, no flags
     OP_RECV_ADAPT = 6,  // mover CTAs: wait for the sender's word; pull peer -> local, or fall back to posting
+    OP_RECV_STAGED = 7, // mover CTAs: this rank's buffer is in no window: ask the sender to go through the staging ring
 };
 
 enum AsyncError : uint32_t { AERR_NONE = 0, AERR_TIMEOUT_POST = 1, AERR_TIMEOUT_DONE = 2,
-                             AERR_TIMEOUT_LL_DATA = 3, AERR_TIMEOUT_LL_ACK = 4, AERR_BAD_WINDOW = 5 };
+                             AERR_TIMEOUT_LL_DATA = 3, AERR_TIMEOUT_LL_ACK = 4, AERR_BAD_WINDOW = 5,
+                             AERR_TIMEOUT_STAGE = 6, AERR_STAGE_BUSY = 7 };
 
 struct alignas(8) OpDesc {
     uint64_t local;      // this GPU's buffer: source of a send, destination of a receive
@@ -61,7 +63,28 @@ struct alignas(8) OpDesc {
     uint32_t peer;
     uint32_t flags;      // OPF_*
     uint32_t pad;
+    uint64_t stage;      // StageInfo of `peer` in local memory (roles that may go through the staging ring)
 };
+
+// Staging ring between one ordered pair of ranks, for receive buffers that are in no window (plain cudaMalloc
+// memory nobody registered, as in the reference, p2p_matrix.cc:127-128): the sender stores chunk c into slot
+// c % slots of a ring in the RECEIVER's control region and publishes `filled`, the receiver copies the chunk out
+// into its buffer and publishes `drained` at the sender.  Both counters are (seq << 24 | chunks), so they never
+// need resetting.  One such message per ordered pair at a time (`lock`, taken by the receiver before it asks).
+struct StageInfo {
+    uint64_t send_ring;     // peer-mapped: the ring in the peer's region that my sends to it go through
+    uint64_t send_filled;   // peer-mapped flag I publish after each chunk
+    uint64_t send_drained;  // local flag the peer publishes when it has copied a chunk out
+    uint64_t send_arrive;   // local u32[slots]: CTAs of the send that have finished the chunk in that slot
+    uint64_t recv_ring;     // local: the ring my receives from this peer come through
+    uint64_t recv_filled;   // local
+    uint64_t recv_drained;  // peer-mapped
+    uint64_t recv_arrive;   // local u32[slots]
+    uint64_t lock;          // local u32
+    uint32_t chunk, slots;
+};
+constexpr int kStageSlots = 4;
+__host__ __device__ __forceinline__ uint64_t stage_count(uint64_t seq, uint64_t chunks) { return (seq << 24) | chunks; }
 
 enum OpFlags : uint32_t {
     OPF_EARLY_POST = 1,  // OP_POST of a send: the word may be published before griddepcontrol.wait when the kernel
@@ -235,8 +258,9 @@ __device__ __forceinline__ void copy_elems(T* __restrict__ dst, const T* __restr
                                            uint32_t part, uint32_t nparts) {
     const size_t stride = (size_t)nparts * blockDim.x;
     size_t i = (size_t)part * blockDim.x + threadIdx.x;
+    // ld.cv: a staging-ring slot is read again and again within one kernel, so nothing of it may linger in L1
 #pragma unroll 4
-    for (; i < n; i += stride) dst[i] = src[i];
+    for (; i < n; i += stride) dst[i] = __ldcv(src + i);
 }
 
 struct Ld16 { __device__ __forceinline__ uint4 operator()(const uint4* p) const { return ld_stream16(p); } };
@@ -253,14 +277,14 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, siz
         size_t head = (16 - ((uint64_t)dst & 15)) & 15;
         if (head > n) head = n;
         if (part == 0)
-            for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = src[i];
+            for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = __ldcv(src + i);
         uint8_t* d = dst + head;
         const uint8_t* s = src + head;
         const size_t left = n - head;
         const size_t body = left & ~(size_t)15;
         copy_vectors<uint4, 8>((uint4*)d, (const uint4*)s, body / 16, part, nparts, Ld16{}, St16{});
         if (part == nparts - 1)
-            for (size_t i = body + threadIdx.x; i < left; i += blockDim.x) d[i] = s[i];
+            for (size_t i = body + threadIdx.x; i < left; i += blockDim.x) d[i] = __ldcv(s + i);
         return;
     }
     // different phase: widest element both sides can be aligned to at once
@@ -268,7 +292,7 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, siz
     size_t head = (w - ((uint64_t)dst & (w - 1))) & (w - 1);
     if (head > n) head = n;
     if (part == 0)
-        for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = src[i];
+        for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = __ldcv(src + i);
     uint8_t* d = dst + head;
     const uint8_t* s = src + head;
     const size_t left = n - head;
@@ -280,7 +304,7 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, siz
         default: copy_elems(d, s, ne, part, nparts); break;
     }
     if (part == nparts - 1)
-        for (size_t i = ne * w + threadIdx.x; i < left; i += blockDim.x) d[i] = s[i];
+        for (size_t i = ne * w + threadIdx.x; i < left; i += blockDim.x) d[i] = __ldcv(s + i);
 }
 
 // ---------------------------------------------------------------- rendezvous roles
@@ -291,6 +315,7 @@ __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, siz
 constexpr uint64_t kPostValid = 1ull << 39;
 constexpr uint64_t kPostOffMask = kPostValid - 1;
 constexpr uint32_t kWinPushPlease = 0xFFu;
+constexpr uint32_t kWinStaged = 0xFEu;  // in a RECEIVER's post: "my buffer is in no window, send through the staging ring"
 __host__ __device__ __forceinline__ uint64_t make_post_word(uint64_t seq, uint32_t win, uint64_t off) {
     return ((seq & 0xffffull) << 48) | ((uint64_t)(win & 0xffu) << 40) | kPostValid | (off & kPostOffMask);
 }
@@ -310,6 +335,7 @@ __device__ __forceinline__ bool wait_word(const GroupHdr& h, const uint64_t* slo
     return spin_flag(slot, h.timeout_ns, word, [tag](uint64_t x) { return (x >> 48) == tag && (x & kPostValid); });
 }
 
+constexpr uint64_t kStagedMarker = 1;  // "destination" of a push whose receiver asked for the staging ring
 // All CTAs of a push learn the destination; returns nullptr on timeout / bad window.
 __device__ __forceinline__ uint8_t* push_wait_post(const GroupHdr& h, const OpDesc& op, uint32_t part, uint64_t* smem_slot) {
     if (threadIdx.x == 0) {
@@ -317,8 +343,9 @@ __device__ __forceinline__ uint8_t* push_wait_post(const GroupHdr& h, const OpDe
         uint64_t v = 0, dst = 0;
         if (wait_word(h, (const uint64_t*)op.f_wait, op.seq, v)) {
             const uint32_t win = (uint32_t)(v >> 40) & 0xffu;
-            const uint64_t base = ((const uint64_t*)op.aux)[win];
-            if (base) dst = base + (v & kPostOffMask);
+            const uint64_t base = win == kWinStaged ? 0 : ((const uint64_t*)op.aux)[win];
+            if (win == kWinStaged) dst = kStagedMarker;
+            else if (base) dst = base + (v & kPostOffMask);
             else report_error(h, AERR_BAD_WINDOW);
         } else {
             report_error(h, AERR_TIMEOUT_POST);
@@ -365,11 +392,9 @@ __device__ __forceinline__ const uint8_t* recv_adaptive(const GroupHdr& h, const
     if (v == 0) return nullptr;
     const uint32_t win = (uint32_t)(v >> 40) & 0xffu;
     if (win == kWinPushPlease) {
+        if (!op.word) return (const uint8_t*)kStagedMarker;  // neither buffer is in a window: the staging ring
         if (threadIdx.x == 0) {
-            if (part == 0) {
-                if (op.word) post_and_wait(h, op);
-                else report_error(h, AERR_BAD_WINDOW);  // neither side's buffer is registered
-            }
+            if (part == 0) post_and_wait(h, op);
             // every CTA of the op has read the sender's word: the last one through clears the slot (see movers_signal)
             const uint32_t old = atomicInc((uint32_t*)op.arrive, op.nblocks - 1);
             if (old == op.nblocks - 1) *(volatile uint64_t*)op.f_wait2 = 0;
@@ -382,6 +407,25 @@ __device__ __forceinline__ const uint8_t* recv_adaptive(const GroupHdr& h, const
         return nullptr;
     }
     return (const uint8_t*)(base + (v & kPostOffMask));
+}
+
+
+// ---------------------------------------------------------------- staging ring (unregistered receive buffers)
+
+struct CopyJob;
+
+// Receiver, before anything else: take the pair's ring (one staged message per ordered pair at a time) and
+// tell the sender to use it.  Done by one thread; the other CTAs go straight to waiting for chunks.
+__device__ __forceinline__ void stage_ask(const GroupHdr& h, const OpDesc& op, uint32_t part) {
+    if (part != 0 || threadIdx.x != 0) return;
+    const StageInfo* st = (const StageInfo*)op.stage;
+    const uint64_t t0 = globaltimer_ns();
+    uint32_t polls = 0;
+    while (atomicCAS((uint32_t*)st->lock, 0u, 1u) != 0u) {
+        __nanosleep(100);
+        if ((++polls & 255u) == 0 && globaltimer_ns() - t0 > h.timeout_ns) { report_error(h, AERR_STAGE_BUSY); return; }
+    }
+    st_release_sys((uint64_t*)op.f_signal, make_post_word(op.seq, kWinStaged, 0));
 }
 
 // ---------------------------------------------------------------- eager (LL) roles
@@ -505,12 +549,71 @@ __device__ __forceinline__ void run_ctrl(const GroupHdr& h, const OpDesc* ops) {
 struct CopyJob {
     uint8_t* dst;
     const uint8_t* src;
+    size_t nbytes;       // bytes of this pass (the message, or one chunk of a staged one)
     uint64_t signal;     // flag the last CTA publishes afterwards (0: none)
     uint64_t consumed;   // local slot the op's tagged word arrived in, zeroed by that last CTA
     const OpDesc* op;
     uint32_t part;
     bool is_push;        // destination is peer memory (the TMA flavour stages these)
+    uint32_t staged;     // 0 direct, 1 sending through the staging ring, 2 receiving through it
+    uint32_t chunk;      // staged: index of the chunk this pass moves
 };
+
+// Staged message, before a chunk is copied: wait until its ring slot may be written (send: the receiver has
+// drained the chunk that used it before) or read (receive: the sender has filled it); point the job at it.
+__device__ __forceinline__ bool stage_begin(const GroupHdr& h, CopyJob& job, uint64_t* smem_slot) {
+    const OpDesc& op = *job.op;
+    const StageInfo* st = (const StageInfo*)op.stage;
+    const uint32_t c = job.chunk;
+    const bool send = job.staged == 1;
+    __syncthreads();  // smem_slot is reused from pass to pass
+    if (threadIdx.x == 0) {
+        uint64_t ok = 1, v;
+        const uint64_t want = send ? stage_count(op.seq, c + 1 - st->slots) : stage_count(op.seq, c + 1);
+        if (!send || c >= st->slots) {
+            const uint64_t* flag = (const uint64_t*)(send ? st->send_drained : st->recv_filled);
+            // counts of this very message only: an older message's count has a smaller sequence number
+            if (!spin_flag(flag, h.timeout_ns, v, [want](uint64_t x) { return x >= want; })) {
+                report_error(h, AERR_TIMEOUT_STAGE);
+                ok = 0;
+            }
+        }
+        *smem_slot = ok;
+    }
+    __syncthreads();
+    if (!*smem_slot) return false;
+    const size_t off = (size_t)c * st->chunk;
+    job.nbytes = op.nbytes - off < st->chunk ? op.nbytes - off : st->chunk;
+    uint8_t* user = (uint8_t*)op.local + off;
+    uint8_t* slot = (uint8_t*)(send ? st->send_ring : st->recv_ring) + (size_t)(c % st->slots) * st->chunk;
+    job.dst = send ? slot : user;
+    job.src = send ? user : slot;
+    return true;
+}
+
+// After the chunk: the last CTA of the op to finish it publishes the count.  Returns true while chunks remain.
+__device__ __forceinline__ bool stage_end(const GroupHdr& h, CopyJob& job) {
+    const OpDesc& op = *job.op;
+    const StageInfo* st = (const StageInfo*)op.stage;
+    const uint32_t c = job.chunk;
+    const bool send = job.staged == 1;
+    const uint32_t nchunks = (uint32_t)((op.nbytes + st->chunk - 1) / st->chunk);
+    const bool last_chunk = c + 1 == nchunks;
+    __syncthreads();
+    if (last_chunk) pdl_trigger_late(h);
+    if (threadIdx.x == 0) {
+        fence_sys();
+        uint32_t* arrive = (uint32_t*)(send ? st->send_arrive : st->recv_arrive) + (c % st->slots);
+        const uint32_t old = atomicInc(arrive, op.nblocks - 1);
+        if (old == op.nblocks - 1) {
+            if (last_chunk && job.consumed) *(volatile uint64_t*)job.consumed = 0;
+            st_release_sys((uint64_t*)(send ? st->send_filled : st->recv_drained), stage_count(op.seq, c + 1));
+            if (last_chunk && !send) atomicExch((uint32_t*)st->lock, 0u);  // the pair's ring is free again
+        }
+    }
+    job.chunk = c + 1;
+    return !last_chunk;
+}
 
 // Runs the control / eager roles to completion and resolves the mover roles to a CopyJob, so
 // that each kernel has exactly one inlined copy loop.  Returns false when this CTA is done.
@@ -525,6 +628,9 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
     job.op = op;
     job.part = part;
     job.is_push = false;
+    job.nbytes = op->nbytes;
+    job.staged = 0;
+    job.chunk = 0;
     switch (op->kind) {
         case OP_PUSH:
             job.dst = push_wait_post(h, *op, part, slot);
@@ -532,6 +638,7 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
             job.signal = op->f_signal;
             job.consumed = op->f_wait;
             job.is_push = true;
+            if ((uint64_t)job.dst == kStagedMarker) { job.staged = 1; job.signal = 0; }
             return job.dst != nullptr;
         case OP_COPY:
             job.dst = (uint8_t*)op->aux;
@@ -544,7 +651,16 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
             job.dst = (uint8_t*)op->local;
             job.signal = op->f_signal2;
             job.consumed = op->f_wait2;
+            if ((uint64_t)job.src == kStagedMarker) { stage_ask(h, *op, part); job.staged = 2; job.signal = 0; }
             return job.src != nullptr;
+        case OP_RECV_STAGED:
+            stage_ask(h, *op, part);
+            job.staged = 2;
+            job.signal = 0;
+            job.consumed = 0;
+            job.dst = (uint8_t*)op->local;
+            job.src = nullptr;
+            return true;
         case OP_SEND_LL: ll_send(h, *op, part, slot); return false;
         case OP_RECV_LL: ll_recv(h, *op, part); return false;
         default: return false;

@@ -65,7 +65,9 @@ struct PeerCtl {
     uint64_t pull_post[kRing];
     uint64_t pull_done[kRing];
     uint64_t ll_ack[kLLSlots];
-    uint64_t pad[8];
+    uint64_t stage_filled;   // written by the peer as sender through my staging ring: (seq << 24 | chunks filled)
+    uint64_t stage_drained;  // written by the peer as receiver of my staged sends: (seq << 24 | chunks copied out)
+    uint64_t pad[6];
 };
 
 // Host mailbox (POSIX shared memory, one per job): the receiver's HOST publishes where a large receive goes at the
@@ -109,11 +111,16 @@ struct Options {
     long long timeout_ms = 20000;
     long long tma_chunk = 32 * 1024;
     long long tma_stages = 6;
+    long long tma_peer_chunk = 64 * 1024;  // ring geometry of launches that move bytes over NVLink: 3 x 64 KiB reaches the
+    long long tma_peer_stages = 3;         // link rate with 32 CTAs (6 x 32 KiB, the best LOCAL copy, needs 96 for a push)
+    long long pull_tma_min_bytes = 8 << 20;  // auto: a large receive at or above this pulls through the TMA ring (cp.async.bulk
+                                             // from the peer: 750-764 GB/s against 738 for the ld/st loop; -1 never)
     long long tma_min_bytes = -1;  // auto: pushes at or above this use the TMA flavour (-1 never)
     long long self_tma_min_bytes = 32 << 20;  // auto: local copies at or above this use the TMA flavour (-1 never)
     long long pdl = 1;             // programmatic dependent launch: 0 never, 1 eager-only and local-copy groups (where it
                                    // measured faster), 2 every group with the trigger at kernel entry (push/pull kernels
-                                   // measured slower with it), 3 every group, mover CTAs trigger after their copy loop
+                                   // measured slower with it), 3 as 1 plus groups of large messages, whose mover CTAs
+                                   // trigger after their copy loop
     long long early_post = 0;      // with pdl 3: a send offered for pulling is published before the kernel ahead of it on the
                                    // stream has retired, when that kernel is the engine's own and does not write the payload
     long long loopback = 0;        // 1: a send to oneself goes through the wire protocol instead of a plain copy (tests)
@@ -128,6 +135,7 @@ struct Options {
                                    // it loses to the pull kernel (256 MiB: 708 vs 726 GB/s streamed, 496 vs 368 us per
                                    // ping-pong hop): kernel -> DMA -> kernel on one stream costs more than the DMA gains.
     long long ce_wait_us = 200;    // how long p2p_send's host side waits for that word before using the SM path
+    long long stage_chunk = 1 << 20;  // bytes per slot of the staging ring (receive buffers that are in no window); same on all ranks
     long long ce_flags = 1;        // who handles the flags around the DMA: 0 two one-thread kernels (round 1), 1 stream memory
                                    // operations (cuStreamWaitValue64 / cuStreamWriteValue64: nothing to launch, so the chain
                                    // may run beside a group's kernel), 2 as 1 but flags in PEER memory are written by 8-byte DMA
@@ -140,7 +148,8 @@ struct Engine {
     uint64_t host_hash = 0;
     Options opt;
 
-    size_t ctl_bytes = 0, ll_slot_bytes = 0, ll_off = 0;
+    size_t ctl_bytes = 0, ll_slot_bytes = 0, ll_off = 0, stage_off = 0;
+    StageInfo* stage_table = nullptr;           // device [nranks], filled in p2p_connect
     uint8_t* ctl = nullptr;                     // my control region (exported)
     uint8_t* peer_ctl[P2P_MAX_RANKS] = {};      // everyone's, peer-mapped (mine == ctl)
     uint32_t* arrive = nullptr;                 // local arrival counters: push [nranks][kRing], pull [nranks][kRing], eager [nranks][kLLSlots]
@@ -285,6 +294,9 @@ const OptionSpec kOptionSpecs[] = {
     {"tma_chunk", "P2P_TMA_CHUNK", &Options::tma_chunk, 1024, 128 * 1024},
     {"tma_stages", "P2P_TMA_STAGES", &Options::tma_stages, 2, kTmaMaxStages},
     {"tma_min_bytes", "P2P_TMA_MIN_BYTES", &Options::tma_min_bytes, -1, 1ll << 40},
+    {"tma_peer_chunk", "P2P_TMA_PEER_CHUNK", &Options::tma_peer_chunk, 1024, 128 * 1024},
+    {"tma_peer_stages", "P2P_TMA_PEER_STAGES", &Options::tma_peer_stages, 2, kTmaMaxStages},
+    {"pull_tma_min_bytes", "P2P_PULL_TMA_MIN_BYTES", &Options::pull_tma_min_bytes, -1, 1ll << 40},
     {"self_tma_min_bytes", "P2P_SELF_TMA_MIN_BYTES", &Options::self_tma_min_bytes, -1, 1ll << 40},
     {"pdl", "P2P_PDL", &Options::pdl, 0, 3},
     {"early_post", "P2P_EARLY_POST", &Options::early_post, 0, 1},
@@ -296,6 +308,7 @@ const OptionSpec kOptionSpecs[] = {
     {"ce_min_bytes", "P2P_CE_MIN_BYTES", &Options::ce_min_bytes, -1, 1ll << 40},
     {"ce_wait_us", "P2P_CE_WAIT_US", &Options::ce_wait_us, 0, 10000000},
     {"ce_flags", "P2P_CE_FLAGS", &Options::ce_flags, 0, 2},
+    {"stage_chunk", "P2P_STAGE_CHUNK", &Options::stage_chunk, 4096, 16 << 20},
 };
 
 const OptionSpec* find_option(const char* name) {
@@ -314,6 +327,10 @@ int validate_option(const OptionSpec& sp, long long value, const Options& o, con
         return fail(P2P_INVALID_ARGUMENT, "%stma_chunk = %lld is not a multiple of 16 (cp.async.bulk alignment)", source, t.tma_chunk);
     if (t.tma_chunk * t.tma_stages > 200 * 1024)
         return fail(P2P_INVALID_ARGUMENT, "%stma ring %lld x %lld bytes exceeds 200 KiB of shared memory", source, t.tma_stages, t.tma_chunk);
+    if (t.tma_peer_chunk % 16)
+        return fail(P2P_INVALID_ARGUMENT, "%stma_peer_chunk = %lld is not a multiple of 16 (cp.async.bulk alignment)", source, t.tma_peer_chunk);
+    if (t.tma_peer_chunk * t.tma_peer_stages > 200 * 1024)
+        return fail(P2P_INVALID_ARGUMENT, "%stma ring %lld x %lld bytes exceeds 200 KiB of shared memory", source, t.tma_peer_stages, t.tma_peer_chunk);
     return P2P_SUCCESS;
 }
 
@@ -436,9 +453,10 @@ inline int self_copy_flavour(size_t nbytes) {
 }
 
 // CTAs that move `nbytes`: `flavour` of the launch, destination class decides the cap
-inline int mover_ctas(size_t nbytes, int flavour, bool self, bool pull, int fanout = 1) {
+inline int mover_ctas(size_t nbytes, int flavour, bool self, bool pull, int fanout = 1, long long tma_chunk = 0) {
     if (flavour == FLAVOUR_TMA && !pull) {
-        const size_t chunks = (nbytes + (size_t)g.opt.tma_chunk - 1) / (size_t)g.opt.tma_chunk;
+        if (tma_chunk <= 0) tma_chunk = g.opt.tma_chunk;
+        const size_t chunks = (nbytes + (size_t)tma_chunk - 1) / (size_t)tma_chunk;
         const long long cap = self ? (g.opt.self_nblocks ? g.opt.self_nblocks : (long long)g.sm_count * g.ctas_tma)
                                    : (g.opt.nblocks ? g.opt.nblocks : 32);
         return (int)std::max<size_t>(1, std::min<size_t>((chunks + 1) / 2, (size_t)cap));  // >= 2 chunks per ring
@@ -472,6 +490,30 @@ bool lookup_window(const void* buf, size_t nbytes, uint32_t* win, uint64_t* off)
 inline uint32_t* arrive_push(int p, uint64_t seq) { return g.arrive + (size_t)p * kRing + seq % kRing; }
 inline uint32_t* arrive_pull(int p, uint64_t seq) { return g.arrive + (size_t)(g.nranks + p) * kRing + seq % kRing; }
 inline uint32_t* arrive_ll(int p, uint64_t seq) { return g.arrive + (size_t)2 * g.nranks * kRing + (size_t)p * kLLSlots + seq % kLLSlots; }
+// staging ring: per peer kStageSlots send counters, kStageSlots receive counters, one lock
+inline size_t arrive_words(int nranks) { return (size_t)nranks * (2 * kRing + kLLSlots + 2 * kStageSlots + 1); }
+inline uint32_t* arrive_stage(int p) { return g.arrive + (size_t)g.nranks * (2 * kRing + kLLSlots) + (size_t)p * (2 * kStageSlots + 1); }
+inline uint8_t* stage_ring(uint8_t* region, int from) { return region + g.stage_off + (size_t)from * kStageSlots * (size_t)g.opt.stage_chunk; }
+
+// Where everything of the staging ring between me and peer p lies, as the kernels need it.
+StageInfo stage_info_for(int p) {
+    StageInfo si;
+    memset(&si, 0, sizeof si);
+    uint8_t* my = g.ctl;
+    uint8_t* theirs = g.peer_ctl[p];
+    si.send_ring = (uint64_t)stage_ring(theirs, g.rank);
+    si.send_filled = (uint64_t)&peer_section(theirs, g.rank)->stage_filled;
+    si.send_drained = (uint64_t)&peer_section(my, p)->stage_drained;
+    si.send_arrive = (uint64_t)arrive_stage(p);
+    si.recv_ring = (uint64_t)stage_ring(my, p);
+    si.recv_filled = (uint64_t)&peer_section(my, p)->stage_filled;
+    si.recv_drained = (uint64_t)&peer_section(theirs, g.rank)->stage_drained;
+    si.recv_arrive = (uint64_t)(arrive_stage(p) + kStageSlots);
+    si.lock = (uint64_t)(arrive_stage(p) + 2 * kStageSlots);
+    si.chunk = (uint32_t)g.opt.stage_chunk;
+    si.slots = kStageSlots;
+    return si;
+}
 
 // ---- group launch --------------------------------------------------------------------
 //
@@ -491,6 +533,7 @@ struct Resolved {
     uint64_t off;
     bool registered;
     bool pull_send;   // large send that lets the receiver pull
+    bool staged;      // receive into a buffer that is in no window, below the pull threshold: through the staging ring
     int nblocks;
     uint64_t seq;
     bool ce;          // large send handed to the copy engine
@@ -499,11 +542,13 @@ struct Resolved {
 
 struct GroupShape {
     int flavour = FLAVOUR_LDST;
+    long long tma_chunk = 32 * 1024, tma_stages = 6;  // ring geometry of this launch (TMA flavour)
     int n_large_sends = 0, n_large_recvs = 0;
     uint32_t n_ctrl = 0;
     size_t eager_total = 0;
     bool only_small = true;
     bool any_ce = false;
+    bool peers = false;   // the group holds operations with other ranks (not only a local copy)
 };
 
 int match_self_pairs(const std::vector<PendingOp>& ops, std::vector<int>& partner) {
@@ -552,12 +597,9 @@ int resolve_protocols(const std::vector<PendingOp>& ops, const std::vector<int>&
         ++nops_out;
         if (r.proto == PROTO_EAGER) continue;
         r.registered = lookup_window(op.buf, op.nbytes, &r.win, &r.off);
-        if (!op.is_send && r.proto == PROTO_PUSH && !r.registered)
-            return fail(P2P_INVALID_USAGE,
-                        "p2p_recv: buffer %p (+%zu bytes) is not inside a registered window; messages between the eager limit "
-                        "(%lld bytes) and the pull threshold (%lld bytes) are stored directly into the receive buffer by the "
-                        "sender and need p2p_register_export/import first",
-                        op.buf, op.nbytes, g.opt.eager_bytes, g.opt.pull_min_bytes);
+        // a receive buffer nobody registered (the reference's plain cudaMalloc, p2p_matrix.cc:127-128) cannot be
+        // stored into by the sender: the payload then goes through the staging ring in this rank's control region
+        if (!op.is_send && r.proto == PROTO_PUSH && !r.registered) r.staged = true;
         if (op.is_send && r.proto == PROTO_LARGE) {
             // The sender decides.  Let the receiver pull when it can map my buffer — except in a plain pairwise
             // exchange (one large send, and a large receive from that same peer in the group), where two pushes
@@ -579,6 +621,17 @@ int resolve_protocols(const std::vector<PendingOp>& ops, const std::vector<int>&
     }
     if (nops_out > (size_t)kMaxGroupOps)
         return fail(P2P_INVALID_USAGE, "a group holds at most %d operations (got %zu)", kMaxGroupOps, nops_out);
+    // A large receive pulls through the bulk-copy ring: cp.async.bulk reads of peer memory run at 750-764 GB/s where
+    // the ld/st loop gets 738 (larger NVLink requests, less header per payload byte).  The whole launch is then of
+    // the TMA flavour; its pushes and copies go through the ring as well.
+    if (g.opt.path == 0 && g.opt.pull_tma_min_bytes >= 0 && shape.flavour == FLAVOUR_LDST)
+        for (size_t i = 0; i < ops.size(); ++i)
+            if (partner[i] < 0 && !ops[i].is_send && res[i].proto == PROTO_LARGE && (long long)ops[i].nbytes >= g.opt.pull_tma_min_bytes)
+                shape.flavour = FLAVOUR_TMA;
+    // ring geometry: launches that cross NVLink want few large stages, pure local copies more and smaller ones
+    shape.peers = peers_in_group;
+    shape.tma_chunk = peers_in_group ? g.opt.tma_peer_chunk : g.opt.tma_chunk;
+    shape.tma_stages = peers_in_group ? g.opt.tma_peer_stages : g.opt.tma_stages;
     return P2P_SUCCESS;
 }
 
@@ -635,7 +688,10 @@ void size_roles(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, G
         const bool self = op.peer == g.rank;
         switch (r.proto) {
             case PROTO_COPY:
-                r.nblocks = op.is_send ? mover_ctas(op.nbytes, shape.flavour, true, false) : 0;
+                r.nblocks = op.is_send ? mover_ctas(op.nbytes, shape.flavour, true, false, 1, shape.tma_chunk) : 0;
+                // beside transfers over NVLink (all-to-all's own block) a local copy is the short job: it must not
+                // take the SMs the link-bound roles need
+                if (shape.peers && !g.opt.self_nblocks) r.nblocks = std::min(r.nblocks, 32);
                 want += r.nblocks;
                 if (op.nbytes > 4096) shape.only_small = false;
                 break;
@@ -646,7 +702,8 @@ void size_roles(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, G
                 break;
             case PROTO_PUSH:
                 shape.only_small = false;
-                if (op.is_send) { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false); want += r.nblocks; }
+                if (op.is_send) { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false, 1, shape.tma_chunk); want += r.nblocks; }
+                else if (r.staged) { r.nblocks = std::min(16, mover_ctas(op.nbytes, FLAVOUR_LDST, self, true)); want += r.nblocks; }
                 else ++shape.n_ctrl;
                 break;
             case PROTO_LARGE:
@@ -654,7 +711,7 @@ void size_roles(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, G
                 if (op.is_send) {
                     if (r.ce) break;  // moved by the copy engine, outside the kernel
                     if (r.pull_send) ++shape.n_ctrl;
-                    else { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false, shape.n_large_sends); want += r.nblocks; }
+                    else { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false, shape.n_large_sends, shape.tma_chunk); want += r.nblocks; }
                 } else {
                     r.nblocks = mover_ctas(op.nbytes, FLAVOUR_LDST, self, true, shape.n_large_recvs);
                     want += r.nblocks;
@@ -692,6 +749,7 @@ void describe_role(const PendingOp& op, const Resolved& r, const PendingOp* copy
     d.peer = (uint32_t)p;
     d.nblocks = (uint32_t)r.nblocks;
     d.seq = seq;
+    d.stage = (uint64_t)(g.stage_table + p);
     if (r.proto == PROTO_COPY) {
         d.kind = OP_COPY;
         d.aux = (uint64_t)copy_partner->buf;
@@ -710,7 +768,7 @@ void describe_role(const PendingOp& op, const Resolved& r, const PendingOp* copy
         d.f_signal = (uint64_t)&peer_section(theirs, me)->post[seq % kRing];
         d.f_wait = (uint64_t)&peer_section(my, p)->done[seq % kRing];
         if (r.proto == PROTO_PUSH) {
-            d.kind = OP_POST;
+            d.kind = r.staged ? OP_RECV_STAGED : OP_POST;
         } else {
             d.kind = OP_RECV_ADAPT;
             d.f_wait2 = (uint64_t)&peer_section(my, p)->pull_post[seq % kRing];
@@ -764,8 +822,8 @@ uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolve
     if (++g.launch_counter == 0) ++g.launch_counter;
     args.h.my_token = g.launch_counter;
     args.h.prev_token = prev ? prev->token : 0;
-    args.h.tma_chunk = (uint32_t)g.opt.tma_chunk;
-    args.h.tma_stages = (uint32_t)g.opt.tma_stages;
+    args.h.tma_chunk = (uint32_t)shape.tma_chunk;
+    args.h.tma_stages = (uint32_t)shape.tma_stages;
     args.h.timeout_ns = (uint64_t)g.opt.timeout_ms * 1000000ull;
     args.h.async_err = g.async_err_dev;
     args.h.n_ctrl = shape.n_ctrl;
@@ -777,7 +835,7 @@ uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolve
             int cls;
             if (r.proto == PROTO_COPY) cls = op.is_send ? 4 : -1;
             else if (r.proto == PROTO_EAGER) cls = op.is_send ? 1 : 2;
-            else if (r.proto == PROTO_PUSH) cls = op.is_send ? 4 : 0;
+            else if (r.proto == PROTO_PUSH) cls = op.is_send ? 4 : r.staged ? 3 : 0;
             else cls = op.is_send ? (r.ce ? -1 : r.pull_send ? 0 : 4) : 3;
             if (cls != pass) continue;
             OpDesc& d = args.ops[args.h.nops++];
@@ -791,11 +849,16 @@ uint32_t build_args(const std::vector<PendingOp>& ops, const std::vector<Resolve
     bool light = true;  // no rendezvous role in the group
     for (uint32_t i = 0; i < args.h.nops; ++i) {
         const uint32_t k = args.ops[i].kind;
-        if (k == OP_POST || k == OP_PUSH || k == OP_RECV_ADAPT) light = false;
+        if (k == OP_POST || k == OP_PUSH || k == OP_RECV_ADAPT || k == OP_RECV_STAGED) light = false;
     }
-    if (shape.any_ce) args.h.pdl = 0;
-    else if (g.opt.pdl >= 2) args.h.pdl = kPdlLaunched | (g.opt.pdl == 3 ? kPdlLateTrigger : 0);
-    else args.h.pdl = (g.opt.pdl == 1 && light) ? kPdlLaunched : 0;
+    bool mid = false;  // a rendezvous message below the pull threshold: those measured slower with PDL (1-2 MiB: +1 us)
+    for (size_t i = 0; i < ops.size(); ++i)
+        if (res[i].proto == PROTO_PUSH) mid = true;
+    if (shape.any_ce || g.opt.pdl == 0) args.h.pdl = 0;
+    else if (light) args.h.pdl = kPdlLaunched;                      // trigger at kernel entry
+    else if (g.opt.pdl == 2) args.h.pdl = kPdlLaunched;
+    else if (g.opt.pdl == 3 && !mid) args.h.pdl = kPdlLaunched | kPdlLateTrigger;  // movers trigger after their copy loop
+    else args.h.pdl = 0;
     // remember this launch as the latest on its stream; the other streams of the group now end in an event wait
     Engine::StreamLast mine;
     mine.token = args.h.my_token;
@@ -906,7 +969,7 @@ int submit(const std::vector<PendingOp>& ops, const std::vector<Resolved>& res, 
     // the peer's chain has run, and the peer's chain may need ours
     if (shape.any_ce) CUDA_TRY(cudaEventRecord(g.ce_fork, launch_stream));
     if (grid > 0) {
-        const int dyn_smem = shape.flavour == FLAVOUR_TMA ? (int)(g.opt.tma_chunk * g.opt.tma_stages) : 0;
+        const int dyn_smem = shape.flavour == FLAVOUR_TMA ? (int)(shape.tma_chunk * shape.tma_stages) : 0;
         CUDA_TRY(launch_group(shape.flavour, args, grid, block, dyn_smem, launch_stream));
         g.stat_launches++;
     }
@@ -1086,12 +1149,14 @@ int p2p_init(int rank, int nranks, int device) {
     g.ll_slot_bytes = (size_t)std::max<long long>(o.eager_bytes, 8) * 2;
     g.ll_slot_bytes = (g.ll_slot_bytes + 255) & ~(size_t)255;
     g.ll_off = (sizeof(PeerCtl) * (size_t)nranks + 4095) & ~(size_t)4095;
-    g.ctl_bytes = g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes;
+    g.stage_off = (g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes + 4095) & ~(size_t)4095;
+    g.ctl_bytes = g.stage_off + (size_t)nranks * kStageSlots * (size_t)o.stage_chunk;
     CUDA_TRY(cudaMalloc(&g.ctl, g.ctl_bytes));
     CUDA_TRY(cudaMemset(g.ctl, 0, g.ctl_bytes));
-    const size_t arrive_words = (size_t)nranks * (2 * kRing + kLLSlots);
-    CUDA_TRY(cudaMalloc(&g.arrive, sizeof(uint32_t) * arrive_words));
-    CUDA_TRY(cudaMemset(g.arrive, 0, sizeof(uint32_t) * arrive_words));
+    CUDA_TRY(cudaMalloc(&g.arrive, sizeof(uint32_t) * arrive_words(nranks)));
+    CUDA_TRY(cudaMemset(g.arrive, 0, sizeof(uint32_t) * arrive_words(nranks)));
+    CUDA_TRY(cudaMalloc(&g.stage_table, sizeof(StageInfo) * (size_t)nranks));
+    CUDA_TRY(cudaMemset(g.stage_table, 0, sizeof(StageInfo) * (size_t)nranks));
     CUDA_TRY(cudaMalloc(&g.win_table, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
     CUDA_TRY(cudaMemset(g.win_table, 0, sizeof(uint64_t) * (size_t)nranks * P2P_MAX_WINDOWS));
     CUDA_TRY(cudaMalloc(&g.tokens, sizeof(uint32_t) * kTokenSlots));
@@ -1109,7 +1174,7 @@ int p2p_init(int rank, int nranks, int device) {
     CUDA_TRY(cudaEventCreateWithFlags(&g.ev_done, cudaEventDisableTiming));
     CUDA_TRY(configure_kernels(200 * 1024));
     CUDA_TRY(occupancy(FLAVOUR_LDST, 0, &g.ctas_ldst));
-    CUDA_TRY(occupancy(FLAVOUR_TMA, (int)(o.tma_chunk * o.tma_stages), &g.ctas_tma));
+    CUDA_TRY(occupancy(FLAVOUR_TMA, (int)std::max(o.tma_chunk * o.tma_stages, o.tma_peer_chunk * o.tma_peer_stages), &g.ctas_tma));
     if (g.ctas_ldst < 1) g.ctas_ldst = 1;
     if (g.ctas_tma < 1) g.ctas_tma = 1;
     CUDA_TRY(cudaDeviceSynchronize());
@@ -1213,6 +1278,11 @@ int p2p_connect(const void* all_blobs) {
         // without it only the copy-engine path is lost; every other path works
         if (b0.hostbox_name[0] && hostbox_open(b0.hostbox_name) != P2P_SUCCESS) g.hostbox = nullptr;
     }
+    if (!g.plan_only) {
+        std::vector<StageInfo> table((size_t)g.nranks);
+        for (int r = 0; r < g.nranks; ++r) table[(size_t)r] = stage_info_for(r);
+        CUDA_TRY(cudaMemcpy(g.stage_table, table.data(), sizeof(StageInfo) * table.size(), cudaMemcpyHostToDevice));
+    }
     g.connected = true;
     return P2P_SUCCESS;
 }
@@ -1257,6 +1327,7 @@ int p2p_finalize(void) {
         g.ctl = nullptr;
         g.arrive = nullptr;
         g.win_table = nullptr;
+        g.stage_table = nullptr;
         g.tokens = nullptr;
         g.stream_last.clear();
         g.launch_counter = 0;
@@ -1287,6 +1358,8 @@ int p2p_finalize(void) {
     cudaFree(g.ctl);
     cudaFree(g.arrive);
     cudaFree(g.win_table);
+    cudaFree(g.stage_table);
+    g.stage_table = nullptr;
     cudaFree(g.tokens);
     g.tokens = nullptr;
     g.stream_last.clear();
@@ -1493,9 +1566,12 @@ int p2p_get_async_error(int* result) {
     } else {
         static const char* const what[] = {"", "send: receiver never posted", "recv: payload never completed",
                                            "eager recv: data never arrived", "eager send: ring slot never freed",
-                                           "send: receiver posted an unknown window"};
+                                           "send: receiver posted an unknown window",
+                                           "staging ring: the other side never filled / drained a chunk",
+                                           "staging ring of this pair still in use by an earlier message (one unregistered "
+                                           "transfer per ordered pair at a time)"};
         *result = code == AERR_BAD_WINDOW ? P2P_INVALID_USAGE : P2P_REMOTE_ERROR;
-        fail(*result, "device reported: %s (code %u, timeout %lld ms)", code < 6 ? what[code] : "?", code,
+        fail(*result, "device reported: %s (code %u, timeout %lld ms)", code < 8 ? what[code] : "?", code,
              g.opt.timeout_ms);
     }
     return P2P_SUCCESS;
@@ -1509,6 +1585,8 @@ int p2p_set_option(const char* name, long long value) {
     if (!sp) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
     if (!strcmp(name, "pull_min_bytes"))
         return fail(P2P_INVALID_USAGE, "pull_min_bytes is agreed between ranks at p2p_connect; set P2P_PULL_MIN_BYTES before p2p_init");
+    if (!strcmp(name, "stage_chunk"))
+        return fail(P2P_INVALID_USAGE, "stage_chunk sizes the control region; set P2P_STAGE_CHUNK before p2p_init (same on all ranks)");
     int rc = validate_option(*sp, value, g.opt, "");
     if (rc) return rc;
     // the rings were sized in p2p_init; the limit can only shrink afterwards, and on every rank alike
@@ -1516,9 +1594,10 @@ int p2p_set_option(const char* name, long long value) {
         return fail(P2P_INVALID_ARGUMENT, "eager_bytes %lld exceeds the ring slot (%zu bytes); set P2P_EAGER_BYTES before p2p_init",
                     value, g.ll_slot_bytes / 2);
     g.opt.*(sp->slot) = value;
-    if ((!strcmp(name, "tma_chunk") || !strcmp(name, "tma_stages")) && !g.plan_only) {
+    if (!strncmp(name, "tma_", 4) && !g.plan_only) {
         int n = 1;
-        if (occupancy(FLAVOUR_TMA, (int)(g.opt.tma_chunk * g.opt.tma_stages), &n) == cudaSuccess && n >= 1) g.ctas_tma = n;
+        const long long smem = std::max(g.opt.tma_chunk * g.opt.tma_stages, g.opt.tma_peer_chunk * g.opt.tma_peer_stages);
+        if (occupancy(FLAVOUR_TMA, (int)smem, &n) == cudaSuccess && n >= 1) g.ctas_tma = n;
     }
     return P2P_SUCCESS;
 }
@@ -1616,7 +1695,9 @@ int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int c
     // P2P_DEBUG_CTL_BASE + r * P2P_DEBUG_CTL_STRIDE, so tests can tell whose memory a flag address points into
     g.ll_slot_bytes = ((size_t)std::max<long long>(o.eager_bytes, 8) * 2 + 255) & ~(size_t)255;
     g.ll_off = (sizeof(PeerCtl) * (size_t)nranks + 4095) & ~(size_t)4095;
-    g.ctl_bytes = g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes;
+    g.stage_off = (g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes + 4095) & ~(size_t)4095;
+    g.ctl_bytes = g.stage_off + (size_t)nranks * kStageSlots * (size_t)o.stage_chunk;
+    g.stage_table = (StageInfo*)0x500000000000ull;
     for (int r = 0; r < nranks; ++r) g.peer_ctl[r] = (uint8_t*)(0x100000000000ull + (uint64_t)r * 0x1000000000ull);
     g.ctl = g.peer_ctl[rank];
     g.arrive = (uint32_t*)0x200000000000ull;

@@ -15,9 +15,13 @@ p2p_group_kernel_ldst(const __grid_constant__ GroupArgsT<MAXOPS> a) {
     __shared__ uint64_t slot;
     CopyJob job;
     if (!resolve_role(a.h, a.ops, &slot, job)) return;
-    copy_bytes(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks);
+    for (;;) {  // one pass, or one per chunk of a message that goes through the staging ring
+        if (job.staged && !stage_begin(a.h, job, &slot)) return;
+        copy_bytes(job.dst, job.src, job.nbytes, job.part, job.op->nblocks);
+        if (!job.staged || !stage_end(a.h, job)) break;
+    }
     if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);
-    else pdl_trigger_late(a.h);
+    else if (!job.staged) pdl_trigger_late(a.h);
 }
 
 // TMA flavour: 128-thread CTAs, a push is staged global -> shared -> peer global by
@@ -36,13 +40,18 @@ p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
     __syncthreads();
     CopyJob job;
     if (!resolve_role(a.h, a.ops, &slot, job)) return;
-    // the ring stages pushes and local copies; a pull (peer -> local) keeps the register loop
-    if ((((uint64_t)job.dst ^ (uint64_t)job.src) & 15) == 0 && job.op->kind != OP_RECV_ADAPT)
-        tma_push(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty);
-    else
-        copy_bytes(job.dst, job.src, job.op->nbytes, job.part, job.op->nblocks);
+    // the ring moves pushes, pulls and local copies whose two sides share their 16-byte phase; anything else, and
+    // the chunks of a message that goes through the staging ring, keep the register loop
+    for (;;) {
+        if (job.staged && !stage_begin(a.h, job, &slot)) return;
+        if (!job.staged && (((uint64_t)job.dst ^ (uint64_t)job.src) & 15) == 0)
+            tma_push(job.dst, job.src, job.nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty);
+        else
+            copy_bytes(job.dst, job.src, job.nbytes, job.part, job.op->nblocks);
+        if (!job.staged || !stage_end(a.h, job)) break;
+    }
     if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);
-    else pdl_trigger_late(a.h);
+    else if (!job.staged) pdl_trigger_late(a.h);
 }
 
 cudaError_t configure_kernels(int max_tma_smem) {

@@ -1,4 +1,5 @@
-// TMA (bulk async copy) flavour of the rendezvous push, for large messages.
+// TMA (bulk async copy) flavour of the movers, for large messages: pushes (local -> peer), pulls (peer -> local)
+// and local copies all go global -> shared -> global through this ring.
 //
 // Per CTA: a ring of `stages` shared-memory buffers.  Warp 0's elected lane is the
 // PRODUCER: cp.async.bulk global -> shared, completion counted on a `full` mbarrier
@@ -76,6 +77,9 @@ __device__ __forceinline__ void tma_push(uint8_t* dst, const uint8_t* src, size_
     const size_t mine = nchunks > part ? (nchunks - part + nparts - 1) / nparts : 0;
 
     if (threadIdx.x == 0) {  // producer
+        // the payload was written through the generic proxy (by this or a peer GPU) and made visible by the flag this
+        // CTA acquired; the bulk loads below read it through the async proxy
+        fence_proxy_async();
         for (size_t k = 0; k < mine; ++k) {
             const uint32_t st = (uint32_t)(k % stages);
             const uint32_t round = (uint32_t)(k / stages);

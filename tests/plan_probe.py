@@ -14,14 +14,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 MAX_OPS = 32
-KINDS = {0: "none", 1: "post", 2: "push", 3: "send_ll", 4: "recv_ll", 5: "copy", 6: "recv_adapt"}
+KINDS = {0: "none", 1: "post", 2: "push", 3: "send_ll", 4: "recv_ll", 5: "copy", 6: "recv_adapt", 7: "recv_staged"}
 CTL_BASE, CTL_STRIDE = 0x100000000000, 0x1000000000
 
 
 class OpDesc(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint64) for n in ("local", "nbytes", "seq", "f_wait", "f_signal", "word", "f_wait2",
                                                "f_signal2", "word2", "aux", "arrive")] + \
-               [(n, ctypes.c_uint32) for n in ("kind", "first_block", "nblocks", "peer", "flags", "pad")]
+               [(n, ctypes.c_uint32) for n in ("kind", "first_block", "nblocks", "peer", "flags", "pad")] + [("stage", ctypes.c_uint64)]
 
 
 class GroupHdr(ctypes.Structure):

@@ -98,15 +98,21 @@ def test_ldst_push_path(eng, n):
 
 @pytest.mark.parametrize("n", [4 << 20, (4 << 20) + 1, (8 << 20) + 48, (32 << 20) - 5])
 @pytest.mark.parametrize("src_off,dst_off", [(0, 0), (16, 48), (3, 19), (5, 6)])
-def test_pull_path(eng, n, src_off, dst_off):
+@pytest.mark.parametrize("tma_from", [-1, 4 << 20], ids=["ldst", "tma"])
+def test_pull_path(eng, n, src_off, dst_off, tma_from):
     """At or above the pull threshold (4 MiB) the receiver loads the payload from the sender's
-    registered buffer.  (Only the loopback run exercises the wire protocol.)"""
+    registered buffer - with the ld/st loop, or through the bulk-copy ring (cp.async.bulk from the peer mapping)
+    when both sides share their 16-byte phase.  (Only the loopback run exercises the wire protocol.)"""
     eng.p2p.set_option("path", eng.p2p.PATH_AUTO)
     eng.p2p.set_option("bidir_push", 0)   # sender and receiver are the same rank here; do not take that for a bidirectional exchange
+    eng.p2p.set_option("pull_tma_min_bytes", tma_from)
     try:
         assert_exact(eng, n, src_off, dst_off)
+        if eng.loopback:
+            assert eng.p2p.get_option("stat_last_flavour") == (2 if tma_from >= 0 else 1)
     finally:
         eng.p2p.set_option("bidir_push", 1)
+        eng.p2p.set_option("pull_tma_min_bytes", 8 << 20)
 
 
 @pytest.mark.parametrize("pdl,early", [(2, 0), (3, 0), (3, 1)])
@@ -151,7 +157,7 @@ def test_pdl_modes_back_to_back(eng, pdl, early, bidir_push):
 
 def test_large_message_fallbacks(eng):
     """Large message with only one side registered: unregistered sender -> it announces a push;
-    unregistered receiver -> pull still works; neither -> reported, not hung."""
+    unregistered receiver -> pull still works (neither: test_unregistered_buffers_go_through_the_staging_ring)."""
     p2p, torch = eng.p2p, eng.torch
     p2p.set_option("path", p2p.PATH_AUTO)
     p2p.set_option("bidir_push", 0)
@@ -332,29 +338,42 @@ def test_alltoall_one_rank(eng, block):
     assert np.all(got[block:] == 0xA5)
 
 
-def test_unregistered_receive_buffer_is_refused(eng):
+@pytest.mark.parametrize("n", [600_000, (1 << 20) + 3, 2 << 20, (4 << 20) - 1, 4 << 20, (6 << 20) + 11, (21 << 20) + 5])
+@pytest.mark.parametrize("src_off,dst_off,send_registered", [(0, 0, False), (3, 5, False), (16, 48, True)])
+def test_unregistered_buffers_go_through_the_staging_ring(eng, n, src_off, dst_off, send_registered):
+    """The reference never registers anything (plain cudaMalloc, p2p_matrix.cc:127-128).  A receive buffer that is
+    in no window cannot be stored into by the sender: the message then goes chunk by chunk through the staging
+    ring in the receiver's control region - below the pull threshold always, above it when the send buffer is in
+    no window either (otherwise the receiver pulls as ever).  21 MiB is more chunks than the ring has slots."""
     if not eng.loopback:
         pytest.skip("a matched self send/recv is a local copy and needs no window")
-    p2p = eng.p2p
-    other = p2p.DeviceBuffer(2 << 20)
+    p2p, torch = eng.p2p, eng.torch
+    p2p.set_option("path", p2p.PATH_AUTO)
+    p2p.set_option("bidir_push", 0)
+    loose_src, loose_dst = p2p.DeviceBuffer(n + 64), p2p.DeviceBuffer(n + 128)
     try:
-        with pytest.raises(p2p.P2PError) as ei:
+        src = eng.src if send_registered else loose_src
+        for rep in range(2):       # twice: the ring's counters carry over from message to message
+            it = 7000 + rep
+            p2p.pattern_fill(src.ptr + src_off, n, SEED, 0, it, eng.stream)
+            loose_dst.tensor().fill_(0xA5)
+            torch.cuda.synchronize()
             with p2p.group():
-                p2p.recv(other.ptr, 2 << 20, p2p.INT8, 0, eng.stream)
-                p2p.send(eng.src.ptr, 2 << 20, p2p.INT8, 0, eng.stream)
-        assert ei.value.code == p2p.INVALID_USAGE and "registered window" in str(ei.value)
-        # nothing was enqueued and no sequence number moved: the next transfer still matches
+                p2p.recv(loose_dst.ptr + dst_off, n, p2p.INT8, 0, eng.stream)
+                p2p.send(src.ptr + src_off, n, p2p.INT8, 0, eng.stream)
+            eng.stream.synchronize()
+            p2p.raise_async_error()
+            got = loose_dst.tensor().cpu().numpy()
+            assert np.array_equal(got[dst_off: dst_off + n], eng.oracle.expected_recv(n, SEED, 0, it)), (n, rep)
+            assert np.all(got[:dst_off] == 0xA5) and np.all(got[dst_off + n:] == 0xA5), "wrote outside the message"
+        # the ordinary paths still work afterwards (flags and counters of the ring do not leak into them)
         assert_exact(eng, 2 << 20)
-        # eager-sized messages need no window
-        it = 4321
-        p2p.pattern_fill(eng.src.ptr, 1000, SEED, 0, it, eng.stream)
-        with p2p.group():
-            p2p.recv(other.ptr, 1000, p2p.INT8, 0, eng.stream)
-            p2p.send(eng.src.ptr, 1000, p2p.INT8, 0, eng.stream)
-        eng.stream.synchronize()
-        assert np.array_equal(other.tensor()[:1000].cpu().numpy(), eng.oracle.expected_recv(1000, SEED, 0, it))
+        assert_exact(eng, (8 << 20) + 16)
     finally:
-        other.free()
+        p2p.set_option("bidir_push", 1)
+        torch.cuda.synchronize()
+        loose_src.free()
+        loose_dst.free()
 
 
 def test_argument_errors(eng):
@@ -374,9 +393,11 @@ def test_argument_errors(eng):
     assert_exact(eng, 4096)
 
 
-def test_missing_peer_times_out_instead_of_hanging(eng):
-    """A receive whose sender never comes reports P2P_REMOTE_ERROR after the timeout.  Run in a
-    process of its own: the unmatched receive leaves that engine's sequence numbers unusable."""
+@pytest.mark.parametrize("nbytes,what", [(2 << 20, "never completed"), (64, "never arrived")])
+def test_missing_peer_times_out_instead_of_hanging(eng, nbytes, what):
+    """A receive whose sender never comes reports P2P_REMOTE_ERROR after the timeout, and the engine then refuses
+    further transfers (its counters and flag rings are no longer consistent) until p2p_finalize.  Run in a process
+    of its own for that reason."""
     from conftest import ROOT, run
     code = r'''
 import importlib, sys
@@ -389,13 +410,19 @@ buf = p2p.DeviceBuffer(2 << 20)
 p2p.register(buf.ptr, buf.nbytes)
 p2p.set_option("timeout_ms", 200)
 s = torch.cuda.Stream()
-p2p.recv(buf.ptr, 2 << 20, p2p.INT8, 0, s)      # rendezvous receive, no matching send
+p2p.recv(buf.ptr, %d, p2p.INT8, 0, s)      # no matching send
 s.synchronize()
 assert p2p.async_error() == p2p.REMOTE_ERROR
-assert "never completed" in p2p.lib().p2p_get_last_error().decode()
-p2p.recv(buf.ptr, 64, p2p.INT8, 0, s)           # eager receive, no matching send
-s.synchronize()
-assert p2p.async_error() == p2p.REMOTE_ERROR
+assert %r in p2p.lib().p2p_get_last_error().decode(), p2p.lib().p2p_get_last_error().decode()
+try:
+    p2p.recv(buf.ptr, 64, p2p.INT8, 0, s)
+    raise SystemExit("a transfer was accepted after a device-side timeout")
+except p2p.P2PError as e:
+    assert e.code == p2p.REMOTE_ERROR and "error state" in str(e), e
+p2p.finalize()
+p2p.init(0, 1, 0)                              # a fresh engine works again
+assert p2p.async_error() == p2p.SUCCESS
+p2p.finalize()
 print("timed out cleanly")
-''' % ROOT
+''' % (ROOT, nbytes, what)
     assert "timed out cleanly" in run(["python", "-c", code], timeout=120).stdout

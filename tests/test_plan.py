@@ -136,11 +136,20 @@ def test_protocol_by_size_and_eager_launch_shape():
     assert [r["ops"][0]["seq"] for r in res] == [1, 2, 3, 4, 1, 2, 3]
 
 
-def test_receive_between_eager_limit_and_pull_threshold_needs_a_window():
+def test_receive_into_an_unregistered_buffer_goes_through_the_staging_ring():
+    """The reference's buffers are plain cudaMalloc memory nobody registered (p2p_matrix.cc:127-128).  Between the
+    eager limit and the pull threshold the sender cannot store into such a receive buffer: the receiver gets mover
+    CTAs of its own and asks for the staging ring instead of posting a window."""
     res = plan(1, 2, [[["recv", LOOSE, 2 * MiB, 0]], [["recv", RECV_WIN, 2 * MiB, 0]], [["recv", LOOSE, 1000, 0]]])
-    assert res[0]["rc"] == 5 and "registered window" in res[0]["error"]          # P2P_INVALID_USAGE, nothing enqueued
-    assert res[1]["rc"] == 0 and res[1]["ops"][0]["kind"] == "post" and res[1]["ops"][0]["seq"] == 1   # the refused call used no number
+    staged = res[0]["ops"][0]
+    assert res[0]["rc"] == 0 and staged["kind"] == "recv_staged" and staged["seq"] == 1 and staged["nblocks"] == 16
+    assert staged["signal_owner"] == 0 and res[0]["n_ctrl"] == 0 and res[0]["grid"] == 16
+    assert res[1]["rc"] == 0 and res[1]["ops"][0]["kind"] == "post" and res[1]["ops"][0]["seq"] == 2
     assert res[2]["rc"] == 0 and res[2]["ops"][0]["kind"] == "recv_ll"
+    # a large message with neither buffer registered: the sender announces a push, the adaptive receive has no
+    # window to post and will ask for the ring on the device
+    (g,) = plan(1, 2, [[["recv", LOOSE, 8 * MiB, 0]]])
+    assert kinds(g) == ["recv_adapt"] and g["ops"][0]["word"] == 0
 
 
 def test_sequence_numbers_follow_program_order_not_role_order():
@@ -185,9 +194,14 @@ def test_alltoall_is_one_group_with_the_local_block_copied():
         if o["kind"] == "push":
             assert o["local"] == SEND_WIN + o["peer"] * blk and o["signal_owner"] == o["peer"]
     assert g["grid"] <= 148 * 2
-    # large blocks: a fan-out, so the peers pull; the local block stays in the ld/st kernel beside them
+    # large blocks: a fan-out, so the peers pull - through the bulk-copy ring, and the local block beside them with
+    # no more CTAs than one flow could use
     (g,) = plan(2, 8, [[["alltoall", SEND_WIN, RECV_WIN, 64 * MiB]]])
-    assert kinds(g).count("recv_adapt") == 7 and kinds(g).count("post") == 7 and g["flavour"] == 1
+    assert kinds(g).count("recv_adapt") == 7 and kinds(g).count("post") == 7 and g["flavour"] == 2
+    assert all(o["nblocks"] == 9 for o in g["ops"] if o["kind"] == "recv_adapt")
+    assert next(o for o in g["ops"] if o["kind"] == "copy")["nblocks"] == 32 and g["grid"] == 1 + 63 + 32 <= 148
+    (g,) = plan(2, 8, [[["alltoall", SEND_WIN, RECV_WIN, 64 * MiB]]], options={"pull_tma_min_bytes": -1})
+    assert g["flavour"] == 1
 
 
 def test_eager_roles_never_take_more_than_half_the_machine():

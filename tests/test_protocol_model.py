@@ -28,7 +28,58 @@ from conftest import ROOT, run
 PROBE = os.path.join(ROOT, "tests", "plan_probe.py")
 SEND_WIN, RECV_WIN = 1 << 32, 1 << 33
 WINDOWS = [[SEND_WIN, 1 << 30], [RECV_WIN, 4 << 30]]
-VALID, OFFMASK, PUSH_PLEASE = 1 << 39, (1 << 39) - 1, 0xFF
+VALID, OFFMASK, PUSH_PLEASE, STAGED = 1 << 39, (1 << 39) - 1, 0xFF, 0xFE
+CTL_BASE, CTL_STRIDE = 0x100000000000, 0x1000000000
+SECTION = (64 * 4 + 4 + 8) * 8            # sizeof(PeerCtl)
+STAGE_FILLED, STAGE_DRAINED = 2080, 2088  # offsets in PeerCtl, after post/done/pull_post/pull_done[64] and ll_ack[4]
+STAGE_CHUNK, STAGE_SLOTS = 1 << 20, 4
+
+
+def ctl_flag(region_rank, section_peer, offset):
+    return CTL_BASE + region_rank * CTL_STRIDE + section_peer * SECTION + offset
+
+
+def stage_count(seq, chunks):
+    return (seq << 24) | chunks
+
+
+def staged_send(world, src, dst, op):
+    """Sender side of the staging ring (stage_begin / stage_end of csrc/p2p_device.cuh, chunk by chunk)."""
+    seq, n = op["seq"], op["nbytes"]
+    drained, filled = ctl_flag(src, dst, STAGE_DRAINED), ctl_flag(dst, src, STAGE_FILLED)
+    nchunks = -(-n // STAGE_CHUNK)
+    for c in range(nchunks):
+        if c >= STAGE_SLOTS:
+            while world.flags.get(drained, 0) < stage_count(seq, c + 1 - STAGE_SLOTS):
+                yield
+        world.ring[("stage", src, dst, c % STAGE_SLOTS)] = (seq, c, op["local"])
+        if c + 1 == nchunks and CLEAR_CONSUMED_SLOTS:
+            world.flags[op["f_wait"]] = 0
+        world.flags[filled] = stage_count(seq, c + 1)
+
+
+def staged_recv(world, dst, src, op, consumed=None):
+    """Receiver side: take the pair's ring, ask the sender to use it, copy chunk after chunk out."""
+    seq, n = op["seq"], op["nbytes"]
+    lock = ("stage_lock", dst, src)
+    while world.flags.get(lock, 0):
+        yield
+    world.flags[lock] = 1
+    world.flags[op["f_signal"]] = (seq & 0xFFFF) << 48 | STAGED << 40 | VALID
+    drained, filled = ctl_flag(src, dst, STAGE_DRAINED), ctl_flag(dst, src, STAGE_FILLED)
+    nchunks = -(-n // STAGE_CHUNK)
+    source = None
+    for c in range(nchunks):
+        while world.flags.get(filled, 0) < stage_count(seq, c + 1):
+            yield
+        got = world.ring[("stage", src, dst, c % STAGE_SLOTS)]
+        assert got[:2] == (seq, c), f"staging slot holds chunk {got[:2]} where {(seq, c)} was expected"
+        source = got[2]
+        if c + 1 == nchunks and consumed is not None and CLEAR_CONSUMED_SLOTS:
+            world.flags[consumed] = 0
+        world.flags[drained] = stage_count(seq, c + 1)
+    world.mem[dst][op["local"]] = ("payload", src, source, n)
+    world.flags[lock] = 0
 MiB = 1 << 20
 CLEAR_CONSUMED_SLOTS = True   # what the device code does; the wrap test below also shows what happens without
 
@@ -83,6 +134,9 @@ def role(world, rank, op):
             world.flags[op["f_signal2"]] = op["word2"]
         while world.tagged(op["f_wait"], seq) is None:
             yield
+        if (world.tagged(op["f_wait"], seq) >> 40) & 0xFF == STAGED:
+            yield from staged_send(world, rank, peer, op)
+            return
         dst = window_local(world.tagged(op["f_wait"], seq))
         world.mem[peer][dst] = ("payload", rank, op["local"], op["nbytes"])
         if CLEAR_CONSUMED_SLOTS:
@@ -92,8 +146,9 @@ def role(world, rank, op):
         while world.tagged(op["f_wait2"], seq) is None:
             yield
         word = world.tagged(op["f_wait2"], seq)
-        if (word >> 40) & 0xFF == PUSH_PLEASE:
-            assert op["word"], "sender wants to push but this buffer is not registered"
+        if (word >> 40) & 0xFF == PUSH_PLEASE and not op["word"]:
+            yield from staged_recv(world, rank, peer, op, consumed=op["f_wait2"])   # neither buffer is in a window
+        elif (word >> 40) & 0xFF == PUSH_PLEASE:
             world.flags[op["f_signal"]] = op["word"]
             while world.flags.get(op["f_wait"], 0) != seq:
                 yield
@@ -104,6 +159,8 @@ def role(world, rank, op):
             if CLEAR_CONSUMED_SLOTS:
                 world.flags[op["f_wait2"]] = 0
             world.flags[op["f_signal2"]] = seq
+    elif k == "recv_staged":
+        yield from staged_recv(world, rank, peer, op)
     elif k == "send_ll":
         if seq > 4:
             while world.flags.get(op["f_wait"], 0) != seq - 4:
@@ -252,3 +309,21 @@ def test_sequence_tag_wraps_after_65536_messages():
             check_phases(2, phases, seeds=(1, 2, 3, 4))
     finally:
         CLEAR_CONSUMED_SLOTS = True
+
+
+def test_unregistered_receive_buffers_go_through_the_staging_ring():
+    """The reference's own situation: plain buffers, nothing registered.  Every size above the eager limit then goes
+    through the staging ring - messages of more chunks than the ring has slots, back to back, both ways at once,
+    and a ring of three ranks."""
+    global SEND_WIN, RECV_WIN
+    keep = SEND_WIN, RECV_WIN
+    try:
+        SEND_WIN, RECV_WIN = 1 << 37, 1 << 38          # outside both windows
+        sizes = [600_000, 1 * MiB, 3 * MiB + 5, 4 * MiB, 9 * MiB, 33 * MiB + 1]
+        check_phases(2, [[(0, 1, n)] for n in sizes] + [[(0, 1, n), (1, 0, n)] for n in sizes], seeds=(1, 2, 3))
+        check_phases(3, [[(0, 1, 6 * MiB), (1, 2, 6 * MiB), (2, 0, 2 * MiB)]] * 3, seeds=(4, 5))
+        # only the receiver unregistered: large messages are pulled as ever, mid-size ones are staged
+        SEND_WIN = keep[0]
+        check_phases(2, [[(0, 1, n)] for n in sizes], seeds=(6,))
+    finally:
+        SEND_WIN, RECV_WIN = keep
