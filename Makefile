@@ -41,9 +41,9 @@ else
 endif
 export MPI_INC MPI_LIB MPIRUN
 
-ENGINE_SRCS := $(CSRC)/p2p_engine.cu $(CSRC)/p2p_kernels.cu
+ENGINE_SRCS := $(CSRC)/p2p_engine.cu $(CSRC)/p2p_kernels.cu $(CSRC)/p2p_symm.cu $(CSRC)/p2p_fdpass.cu
 ENGINE_HDRS := include/p2p.h $(CSRC)/p2p_debug.h $(CSRC)/p2p_internal.h $(CSRC)/p2p_device.cuh $(CSRC)/p2p_tma.cuh
-ENGINE_OBJS := $(BUILD)/p2p_engine.o $(BUILD)/p2p_kernels.o
+ENGINE_OBJS := $(BUILD)/p2p_engine.o $(BUILD)/p2p_kernels.o $(BUILD)/p2p_symm.o $(BUILD)/p2p_fdpass.o
 
 all: $(LIBDIR)/libb200p2p.so p2p_matrix mpirun-link
 	@echo "built with: $(MPI_LABEL)"
@@ -98,4 +98,16 @@ clean:
 	$(MAKE) -C third_party/minimpi clean
 	-$(MAKE) -C oracle clean
 
-.PHONY: all oracle tests sass clean mpirun-link
+.PHONY: all oracle tests sass clean mpirun-link experiments
+
+# experiments and profiling harnesses (not part of the product; see scripts/README.md)
+experiments: $(BUILD)/exp_probe $(BUILD)/exp_peer_bw $(BUILD)/prof_peer
+$(BUILD)/exp_probe: scripts/exp_probe.cu
+	@mkdir -p $(BUILD)
+	$(NVCC) $(ARCH) -std=c++17 -O3 -o $@ $< -L$(CUDA_HOME)/lib64/stubs -lcuda
+$(BUILD)/exp_peer_bw: scripts/exp_peer_bw.cu
+	@mkdir -p $(BUILD)
+	$(NVCC) $(ARCH) -std=c++20 -O3 -o $@ $<
+$(BUILD)/prof_peer: scripts/prof_peer.cu $(BUILD)/libb200p2p.a $(ENGINE_HDRS)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(ARCH) -std=c++17 -O3 -lineinfo -Iinclude -I$(CSRC) -o $@ $< $(BUILD)/libb200p2p.a

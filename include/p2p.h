@@ -160,6 +160,33 @@ P2P_API int p2p_group_end(void);
  *      register both buffers. ---- */
 P2P_API int p2p_alltoall(const void* sendbuf, void* recvbuf, size_t count, int dtype, p2p_stream_t stream);
 
+/* ---- symmetric windows on the driver's virtual memory API, and one-to-many over NVSwitch multicast
+ *      (SURVEY section 8, rows f2 and f3).  p2p_register_* shares cudaMalloc memory through cudaIpc handles;
+ *      this allocates instead: `bytes` of device memory on EVERY rank (cuMemCreate), exported as a POSIX
+ *      file descriptor — handed to the peers' processes over a Unix-domain socket inside the library — or,
+ *      with P2P_SYMM_HANDLE=fabric, as a fabric handle (CU_MEM_HANDLE_TYPE_FABRIC: plain bytes, the form that
+ *      also crosses hosts within one NVLink domain).  Collective and two-phase like registration; the result is
+ *      a window p2p_send/p2p_recv use like any other (stands in for ncclMemAlloc + ncclCommWindowRegister,
+ *      nccl.h:130,251).  Where the fabric supports multicast the ranks' parts are also bound to one multicast
+ *      object (cuMulticastCreate), which p2p_bcast stores into. ---- */
+P2P_API size_t p2p_symm_blob_bytes(void);   /* 256 */
+P2P_API int p2p_symm_alloc_export(size_t bytes, void* blob);
+P2P_API int p2p_symm_alloc_import(const void* all_blobs, void** ptr, int* window_id);
+P2P_API int p2p_symm_free(int window_id);   /* collective by convention, like p2p_deregister */
+/* The window's multicast mapping (NULL when there is none): a store through it lands at the same offset of
+ * every rank's part.  For callers who issue multimem instructions from kernels of their own. */
+P2P_API int p2p_symm_multicast_ptr(int window_id, void** mc_ptr);
+/* Broadcast, argument order of ncclBroadcast (nccl.h: sendbuff, recvbuff, count, datatype, root, comm, stream).
+ * The reference has no one-to-many call: its loop shape reaches N-1 receivers with N-1 ncclSend calls
+ * (p2p_matrix.cc:141-172), i.e. the root's link carries the payload N-1 times.  Here the root stores it ONCE,
+ * with multimem.st into the multicast mapping, and the switch replicates it into every rank's `recvbuf`
+ * (the root's own included); completion is published the same way.  Collective: every rank calls it with the
+ * same count, dtype and root; `recvbuf` lies in a symmetric window at the same offset on every rank; `sendbuf`
+ * is read on the root only (any device memory there; may equal recvbuf).  Stream-ordered like p2p_recv: a
+ * receiver's stream holds until the payload has landed, the root's until it has been sent.  Without multicast
+ * (P2P_NO_MULTICAST=1, or a fabric that has none) the root stores to each receiver in turn. ---- */
+P2P_API int p2p_bcast(const void* sendbuf, void* recvbuf, size_t count, int dtype, int root, p2p_stream_t stream);
+
 /* ---- errors: ncclGetErrorString / ncclGetLastError / ncclCommGetAsyncError
  *      (nccl.h:215,219,227) ---- */
 P2P_API const char* p2p_get_error_string(int result);

@@ -78,6 +78,28 @@ static inline int p2p_register_mpi(MPI_Comm comm, void* buf, size_t bytes, int* 
     return rc;
 }
 
+/* Collective: a symmetric window of `bytes` on every rank (ncclMemAlloc + ncclCommWindowRegister in one). */
+static inline int p2p_symm_alloc_mpi(MPI_Comm comm, size_t bytes, void** ptr, int* window_id) {
+    int size = 0, rc;
+    if (MPI_Comm_size(comm, &size) != MPI_SUCCESS) return P2P_SYSTEM_ERROR;
+    char mine[256];
+    char* all = (char*)calloc((size_t)size, sizeof mine);
+    if (!all) return P2P_SYSTEM_ERROR;
+    rc = p2p_symm_alloc_export(bytes, mine);
+    int ok = (rc == P2P_SUCCESS), all_ok = 0;
+    if (MPI_Allreduce(&ok, &all_ok, 1, MPI_INT, MPI_MIN, comm) != MPI_SUCCESS) all_ok = 0;
+    if (all_ok) {
+        if (MPI_Allgather(mine, (int)sizeof mine, MPI_BYTE, all, (int)sizeof mine, MPI_BYTE, comm) != MPI_SUCCESS)
+            rc = P2P_SYSTEM_ERROR;
+        else
+            rc = p2p_symm_alloc_import(all, ptr, window_id);
+    } else if (rc == P2P_SUCCESS) {
+        rc = P2P_REMOTE_ERROR;
+    }
+    free(all);
+    return rc;
+}
+
 /* Collective teardown: close every mapping of peer memory, wait for all ranks to have done so,
  * then free this rank's own regions (stands in for ncclCommDestroy, p2p_matrix.cc:270). */
 static inline int p2p_finalize_mpi(MPI_Comm comm) {

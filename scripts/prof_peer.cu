@@ -5,6 +5,7 @@
 //   push   p2p_group_kernel_ldst, mover role on GPU 0: local LDG.E.128 -> STG.E.128 into GPU 1's memory
 //   pull   p2p_group_kernel_ldst, mover role on GPU 1: LDG.E.128 from GPU 0's memory -> local STG
 //   tma    p2p_group_kernel_tma on GPU 0: cp.async.bulk local -> shared -> GPU 1's memory
+//   tmapull p2p_group_kernel_tma on GPU 1: cp.async.bulk GPU 0's memory -> shared -> local
 //   ll     eager path: OP_SEND_LL on GPU 0 writes flagged 16-byte lines into a ring in GPU 1's memory,
 //          OP_RECV_LL on GPU 1 copies them out (the 8-byte latency path)
 //
@@ -13,7 +14,7 @@
 //
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo -Iinclude -Itest-nccl-p2p_b200/csrc \
 //             -o build/prof_peer scripts/prof_peer.cu build/libb200p2p.a
-// run:   build/prof_peer <push|pull|tma|ll> [bytes] [ctas] [iters]
+// run:   build/prof_peer <push|pull|tma|tmapull|ll> [bytes] [ctas] [iters]
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -48,8 +49,8 @@ int main(int argc, char** argv) {
     GroupArgs a;
     memset(&a, 0, sizeof a);
     a.h.nops = 1;
-    a.h.tma_chunk = 32 * 1024;
-    a.h.tma_stages = 6;
+    a.h.tma_chunk = 64 * 1024;   // the engine's geometry for launches that cross NVLink
+    a.h.tma_stages = 3;
     a.h.timeout_ns = 2000000000ull;
     OpDesc& op = a.ops[0];
     op.nbytes = bytes;
@@ -61,10 +62,11 @@ int main(int argc, char** argv) {
         if (!ctas) ctas = 32;
         op.kind = OP_COPY; op.local = (uint64_t)b0; op.aux = (uint64_t)b1; op.nblocks = ctas;
         if (!strcmp(mode, "tma")) flavour = FLAVOUR_TMA;
-    } else if (!strcmp(mode, "pull")) {
+    } else if (!strcmp(mode, "pull") || !strcmp(mode, "tmapull")) {
         if (!ctas) ctas = 64;
         dev = 1; s = s1;
         op.kind = OP_COPY; op.local = (uint64_t)b0; op.aux = (uint64_t)b1; op.nblocks = ctas;
+        if (!strcmp(mode, "tmapull")) flavour = FLAVOUR_TMA;
     } else if (!strcmp(mode, "ll")) {
         if (bytes > (512 << 10)) bytes = 8;
         op.nbytes = bytes;

@@ -34,6 +34,7 @@ SYMBOLS = [
     "p2p_init", "p2p_blob_bytes", "p2p_export", "p2p_connect", "p2p_disconnect", "p2p_finalize", "p2p_rank", "p2p_nranks",
     "p2p_register_blob_bytes", "p2p_register_export", "p2p_register_import", "p2p_deregister",
     "p2p_mem_alloc", "p2p_mem_free", "p2p_send", "p2p_recv", "p2p_group_start", "p2p_group_end", "p2p_alltoall",
+    "p2p_symm_blob_bytes", "p2p_symm_alloc_export", "p2p_symm_alloc_import", "p2p_symm_free", "p2p_symm_multicast_ptr", "p2p_bcast",
     "p2p_get_error_string", "p2p_get_last_error", "p2p_get_async_error", "p2p_set_option", "p2p_get_option",
     "p2p_query_plan", "p2p_pattern_fill", "p2p_pattern_check", "p2p_digest", "p2p_digest_noalloc",
 ]
@@ -79,6 +80,12 @@ def lib() -> ctypes.CDLL:
         "p2p_send": (i32, [vp, sz, i32, i32, vp]),
         "p2p_recv": (i32, [vp, sz, i32, i32, vp]),
         "p2p_alltoall": (i32, [vp, vp, sz, i32, vp]),
+        "p2p_symm_blob_bytes": (sz, []),
+        "p2p_symm_alloc_export": (i32, [sz, vp]),
+        "p2p_symm_alloc_import": (i32, [vp, ctypes.POINTER(vp), ctypes.POINTER(i32)]),
+        "p2p_symm_free": (i32, [i32]),
+        "p2p_symm_multicast_ptr": (i32, [i32, ctypes.POINTER(vp)]),
+        "p2p_bcast": (i32, [vp, vp, sz, i32, i32, vp]),
         "p2p_group_start": (i32, []),
         "p2p_group_end": (i32, []),
         "p2p_get_error_string": (ctypes.c_char_p, [i32]),
@@ -211,6 +218,43 @@ def recv(ptr: int, count: int, dtype: int, peer: int, stream=None) -> None:
 def alltoall(send_ptr: int, recv_ptr: int, count: int, dtype: int, stream=None) -> None:
     """Block p of the send buffer to rank p, block p of the receive buffer from rank p; one fused launch."""
     check(lib().p2p_alltoall(ctypes.c_void_p(send_ptr), ctypes.c_void_p(recv_ptr), count, dtype, _stream_ptr(stream)))
+
+
+class SymmBuffer:
+    """A symmetric window: `nbytes` on every rank from the driver's virtual memory API, peers mapped, bound to the
+    NVSwitch multicast object when there is one.  Collective."""
+
+    def __init__(self, nbytes: int, allgather: Allgather = _single):
+        L = lib()
+        n = L.p2p_symm_blob_bytes()
+        mine = ctypes.create_string_buffer(n)
+        check(L.p2p_symm_alloc_export(nbytes, mine))
+        blobs = allgather(mine.raw)
+        joined = ctypes.create_string_buffer(b"".join(blobs), n * len(blobs))
+        p, win = ctypes.c_void_p(), ctypes.c_int(-1)
+        check(L.p2p_symm_alloc_import(joined, ctypes.byref(p), ctypes.byref(win)))
+        self.ptr, self.nbytes, self.window = p.value or 0, nbytes, win.value
+        mc = ctypes.c_void_p()
+        check(L.p2p_symm_multicast_ptr(self.window, ctypes.byref(mc)))
+        self.multicast_ptr = mc.value or 0
+
+    @property
+    def __cuda_array_interface__(self):
+        return {"shape": (self.nbytes,), "typestr": "|u1", "data": (self.ptr, False), "version": 3, "strides": None}
+
+    def tensor(self):
+        import torch
+        return torch.as_tensor(self, device="cuda")
+
+    def free(self) -> None:
+        if self.window >= 0:
+            check(lib().p2p_symm_free(self.window))
+            self.window = -1
+
+
+def bcast(send_ptr: int, recv_ptr: int, count: int, dtype: int, root: int, stream=None) -> None:
+    """ncclBroadcast's argument order; recv_ptr lies in a SymmBuffer at the same offset on every rank."""
+    check(lib().p2p_bcast(ctypes.c_void_p(send_ptr), ctypes.c_void_p(recv_ptr), count, dtype, root, _stream_ptr(stream)))
 
 
 def group_start() -> None:

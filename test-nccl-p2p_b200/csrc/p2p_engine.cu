@@ -113,15 +113,15 @@ struct Options {
     long long tma_stages = 6;
     long long tma_peer_chunk = 64 * 1024;  // ring geometry of launches that move bytes over NVLink: 3 x 64 KiB reaches the
     long long tma_peer_stages = 3;         // link rate with 32 CTAs (6 x 32 KiB, the best LOCAL copy, needs 96 for a push)
-    long long pull_tma_min_bytes = 8 << 20;  // auto: a large receive at or above this pulls through the TMA ring (cp.async.bulk
-                                             // from the peer: 750-764 GB/s against 738 for the ld/st loop; -1 never)
+    long long pull_tma_min_bytes = 32 << 20;  // auto: a large receive at or above this, in a group that is also being pulled
+                                              // from, goes through the TMA ring (-1 never); see resolve_protocols
     long long tma_min_bytes = -1;  // auto: pushes at or above this use the TMA flavour (-1 never)
     long long self_tma_min_bytes = 32 << 20;  // auto: local copies at or above this use the TMA flavour (-1 never)
-    long long pdl = 1;             // programmatic dependent launch: 0 never, 1 eager-only and local-copy groups (where it
+    long long pdl = 3;             // programmatic dependent launch: 0 never, 1 eager-only and local-copy groups (where it
                                    // measured faster), 2 every group with the trigger at kernel entry (push/pull kernels
                                    // measured slower with it), 3 as 1 plus groups of large messages, whose mover CTAs
                                    // trigger after their copy loop
-    long long early_post = 0;      // with pdl 3: a send offered for pulling is published before the kernel ahead of it on the
+    long long early_post = 1;      // with pdl 3: a send offered for pulling is published before the kernel ahead of it on the
                                    // stream has retired, when that kernel is the engine's own and does not write the payload
     long long loopback = 0;        // 1: a send to oneself goes through the wire protocol instead of a plain copy (tests)
     long long bidir_push = 1;      // a lone large send pushes instead of offering a pull when its group also holds a large
@@ -621,13 +621,21 @@ int resolve_protocols(const std::vector<PendingOp>& ops, const std::vector<int>&
     }
     if (nops_out > (size_t)kMaxGroupOps)
         return fail(P2P_INVALID_USAGE, "a group holds at most %d operations (got %zu)", kMaxGroupOps, nops_out);
-    // A large receive pulls through the bulk-copy ring: cp.async.bulk reads of peer memory run at 750-764 GB/s where
-    // the ld/st loop gets 738 (larger NVLink requests, less header per payload byte).  The whole launch is then of
-    // the TMA flavour; its pushes and copies go through the ring as well.
-    if (g.opt.path == 0 && g.opt.pull_tma_min_bytes >= 0 && shape.flavour == FLAVOUR_LDST)
-        for (size_t i = 0; i < ops.size(); ++i)
-            if (partner[i] < 0 && !ops[i].is_send && res[i].proto == PROTO_LARGE && (long long)ops[i].nbytes >= g.opt.pull_tma_min_bytes)
-                shape.flavour = FLAVOUR_TMA;
+    // Traffic in both directions at once - this rank pulls a large message while a peer pulls one from it (ring step,
+    // all-pairs) - goes through the bulk-copy ring: cp.async.bulk reads of peer memory put larger requests on the
+    // link than the ld/st loop, which leaves more of the reverse direction to the other flow's payload (two B200s,
+    // 256 MiB both ways: 1269-1285 GB/s against 1216; one way alone the two tie at 741-751 and the ld/st loop starts
+    // faster).  Not when this rank pushes: the push then decides the flavour.
+    if (g.opt.path == 0 && g.opt.pull_tma_min_bytes >= 0 && shape.flavour == FLAVOUR_LDST) {
+        bool pulls = false, offers = false, pushes = false;
+        for (size_t i = 0; i < ops.size(); ++i) {
+            if (partner[i] >= 0 || res[i].proto != PROTO_LARGE) continue;
+            if (!ops[i].is_send) pulls = pulls || (long long)ops[i].nbytes >= g.opt.pull_tma_min_bytes;
+            else if (res[i].pull_send) offers = true;
+            else pushes = true;
+        }
+        if (pulls && offers && !pushes) shape.flavour = FLAVOUR_TMA;
+    }
     // ring geometry: launches that cross NVLink want few large stages, pure local copies more and smaller ones
     shape.peers = peers_in_group;
     shape.tma_chunk = peers_in_group ? g.opt.tma_peer_chunk : g.opt.tma_chunk;
@@ -1108,6 +1116,46 @@ int allocation_range(void* ptr, uint8_t** base, size_t* size) {
 }  // namespace
 }  // namespace p2p
 
+namespace p2p {
+
+int engine_info(EngineInfo* out) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    if (g.plan_only) return fail(P2P_INVALID_USAGE, "not available in plan-only mode");
+    out->rank = g.rank;
+    out->nranks = g.nranks;
+    out->device = g.device;
+    out->sm_count = g.sm_count;
+    out->async_err = g.async_err_dev;
+    out->timeout_ns = (uint64_t)g.opt.timeout_ms * 1000000ull;
+    return P2P_SUCCESS;
+}
+
+int engine_add_window(uint8_t* base, size_t bytes, uint8_t* const* peer_bases, int* window_id) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    int w = -1;
+    for (int i = 0; i < P2P_MAX_WINDOWS; ++i)
+        if (!g.windows[i].used) { w = i; break; }
+    if (w < 0) return fail(P2P_INVALID_USAGE, "all %d windows are in use", P2P_MAX_WINDOWS);
+    Window W;
+    W.used = true;
+    W.base = base;
+    W.bytes = bytes;
+    for (int r = 0; r < g.nranks; ++r) {
+        W.peer_base[r] = peer_bases[r];
+        const uint64_t b = (uint64_t)peer_bases[r];
+        CUDA_TRY(cudaMemcpy(g.win_table + (size_t)r * P2P_MAX_WINDOWS + w, &b, sizeof b, cudaMemcpyHostToDevice));
+    }
+    g.windows[w] = W;
+    *window_id = w;
+    return P2P_SUCCESS;
+}
+
+}  // namespace p2p
+
 using namespace p2p;
 
 // ======================================================================== C ABI
@@ -1337,6 +1385,7 @@ int p2p_finalize(void) {
         return P2P_SUCCESS;
     }
     disconnect_locked();  // a no-op when p2p_disconnect has run
+    symm_finalize(g.nranks);
     for (int r = 0; r < P2P_MAX_RANKS; ++r) {
         g.peer_ctl[r] = nullptr;
         g.rdv_send_seq[r] = g.rdv_recv_seq[r] = g.ll_send_seq[r] = g.ll_recv_seq[r] = 0;

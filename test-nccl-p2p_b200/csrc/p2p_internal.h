@@ -45,6 +45,30 @@ struct CheckPartial {
 // records the text p2p_get_last_error() returns (this thread) and hands `code` back
 int set_last_error(int code, const char* fmt, ...);
 
+// ---- what p2p_symm.cu (VMM windows, multicast broadcast) needs from the engine in p2p_engine.cu ----
+struct EngineInfo {
+    int rank, nranks, device, sm_count;
+    uint32_t* async_err;   // host-mapped word the kernels report into
+    uint64_t timeout_ns;
+};
+int engine_info(EngineInfo* out);  // P2P_INVALID_USAGE unless p2p_init + p2p_connect have run
+// A window whose peer mappings the caller made itself (VMM handles instead of cudaIpc); usable by p2p_send/p2p_recv
+// like any other.  p2p_deregister / p2p_finalize forget it without unmapping anything.
+int engine_add_window(uint8_t* base, size_t bytes, uint8_t* const* peer_bases, int* window_id);
+void symm_finalize(int nranks);    // unmaps and releases every symmetric window (called by p2p_finalize)
+
+// ---- passing POSIX file descriptors between the ranks' processes (p2p_fdpass.cu) ----
+// A CUDA VMM handle exported as a file descriptor means nothing in another process until the descriptor itself
+// has been sent there over a Unix-domain socket (SCM_RIGHTS).  The exporting rank runs a short-lived server thread:
+//   fdpass_serve   starts it for `nfds` descriptors and `requests` expected requests; `name_out` (at least 40 bytes)
+//                  receives the abstract socket name to publish in the rank's blob
+//   fdpass_fetch   connects to a peer's server and returns a duplicate of its descriptor `which` (or -1)
+//   fdpass_finish  waits for the server thread (all expected requests served, or the timeout) and closes the socket
+struct FdServer;
+FdServer* fdpass_serve(const int* fds, int nfds, int requests, int timeout_ms, char* name_out);
+int fdpass_fetch(const char* name, int which, int timeout_ms);
+void fdpass_finish(FdServer* server);
+
 cudaError_t configure_kernels(int max_tma_smem);
 cudaError_t occupancy(int flavour, int dyn_smem, int* ctas_per_sm);
 cudaError_t launch_group(int flavour, const GroupArgs& args, uint32_t grid, uint32_t block, int dyn_smem, cudaStream_t stream);

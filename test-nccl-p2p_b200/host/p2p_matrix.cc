@@ -18,7 +18,10 @@ struct EngineBackend {
     // large messages, load from the send buffer (pull)
     void buffers(void* send, size_t sbytes, void* recv, size_t rbytes) {
         int win = -1;
-        P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, recv, rbytes, &win));
+        // P2P_NO_WINDOWS: exactly the reference's lines, nothing registered (everything above the eager limit then
+        // goes through the staging ring); P2P_NO_SEND_WINDOW: only the receive buffer is a window
+        if (getenv("P2P_NO_WINDOWS")) return;
+        if (!getenv("P2P_NO_RECV_WINDOW")) P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, recv, rbytes, &win));
         if (!getenv("P2P_NO_SEND_WINDOW")) P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, send, sbytes, &win));
     }
 

@@ -112,10 +112,10 @@ def test_pull_path(eng, n, src_off, dst_off, tma_from):
             assert eng.p2p.get_option("stat_last_flavour") == (2 if tma_from >= 0 else 1)
     finally:
         eng.p2p.set_option("bidir_push", 1)
-        eng.p2p.set_option("pull_tma_min_bytes", 8 << 20)
+        eng.p2p.set_option("pull_tma_min_bytes", 32 << 20)
 
 
-@pytest.mark.parametrize("pdl,early", [(2, 0), (3, 0), (3, 1)])
+@pytest.mark.parametrize("pdl,early", [(0, 0), (1, 0), (2, 0), (3, 0), (3, 1)])
 @pytest.mark.parametrize("bidir_push", [0, 1])
 def test_pdl_modes_back_to_back(eng, pdl, early, bidir_push):
     """Programmatic dependent launch for every group (trigger at kernel entry, or after the copy loop), with and
@@ -150,8 +150,8 @@ def test_pdl_modes_back_to_back(eng, pdl, early, bidir_push):
                 assert np.array_equal(got[offs[k]: offs[k] + n], want), (pdl, early, k, n)
                 assert np.all(got[offs[k] + n: offs[k] + n + 64] == 0xA5), "wrote past the end of a message"
     finally:
-        p2p.set_option("pdl", 1)
-        p2p.set_option("early_post", 0)
+        p2p.set_option("pdl", 3)
+        p2p.set_option("early_post", 1)
         p2p.set_option("bidir_push", 1)
 
 

@@ -47,7 +47,7 @@ def test_one_way_large_message_is_pulled_by_the_receiver():
     (g,) = plan(0, 2, [[["send", SEND_WIN, n, 1]]])
     (op,) = g["ops"]
     # sender: one control thread publishes where the payload lies, then waits until it has been read
-    assert (op["kind"], g["grid"], g["n_ctrl"], g["pdl"]) == ("post", 1, 1, 0)
+    assert (op["kind"], g["grid"], g["n_ctrl"], g["pdl"]) == ("post", 1, 1, 3)   # PDL, movers trigger after their copy
     assert op["f_signal"] == flag(1, 0, "pull_post", 1) and op["f_wait"] == flag(0, 1, "pull_done", 1)
     assert op["word"] >> 48 == 1 and (op["word"] >> 40) & 0xFF == 0 and op["word"] & VALID and op["word"] & (VALID - 1) == 0
     (g,) = plan(1, 2, [[["recv", RECV_WIN + 4096, n, 0]]])
@@ -127,7 +127,7 @@ def test_protocol_by_size_and_eager_launch_shape():
     res = plan(0, 2, groups)
     got = [(r["ops"][0]["kind"], r["ops"][0]["nblocks"], r["block"], r["pdl"]) for r in res]
     assert got == [("send_ll", 1, 128, 1), ("send_ll", 1, 128, 1), ("send_ll", 1, 512, 1), ("send_ll", 16, 512, 1),
-                   ("push", 9, 512, 0), ("push", 32, 512, 0), ("post", 0, 512, 0)]
+                   ("push", 9, 512, 0), ("push", 32, 512, 0), ("post", 0, 512, 3)]
     # eager messages go to the ring slot of (sender, seq) in the RECEIVER's region and poll the ack in ours
     first = res[0]["ops"][0]
     assert first["seq"] == 1 and first["wait_owner"] == 0 and first["f_wait"] == flag(0, 1, "ll_ack", 1, ring=4)
@@ -303,7 +303,7 @@ def test_ring_policy_option_makes_the_lone_send_push():
 
 
 def test_early_post_only_when_the_launch_ahead_cannot_be_writing_the_payload():
-    """With pdl 3 + early_post a send offered for pulling may be published while the engine launch ahead of it
+    """With pdl 3 + early_post (the defaults) a send offered for pulling may be published while the engine launch ahead of it
     on the same stream is still running - unless that launch receives into the bytes being sent."""
     n = 16 * MiB
     groups = [[["send", SEND_WIN, n, 1]],                      # nothing ahead: no early post
@@ -311,14 +311,15 @@ def test_early_post_only_when_the_launch_ahead_cannot_be_writing_the_payload():
               [["recv", RECV_WIN, n, 1]],
               [["send", RECV_WIN + 4096, n, 1]],               # forwards what the launch ahead receives: must wait
               [["send", SEND_WIN, n, 1]]]
-    res = plan(0, 2, groups, options={"pdl": 3, "early_post": 1})
+    res = plan(0, 2, groups)                                   # the default: pdl 3, early_post 1
     flags = [r["ops"][0]["flags"] for r in res]
     assert flags == [0, 1, 0, 0, 1]
     assert [r["pdl"] for r in res] == [3] * 5
     assert [r["prev_token"] for r in res] == [0] + [r["my_token"] for r in res[:-1]]
-    # off by default
-    res = plan(0, 2, groups)
-    assert all(r["ops"][0]["flags"] == 0 for r in res) and all(r["pdl"] == 0 for r in res)
+    for opts in ({"early_post": 0}, {"pdl": 1}, {"pdl": 0}):
+        res = plan(0, 2, groups, options=opts)
+        assert all(r["ops"][0]["flags"] == 0 for r in res), opts
+    assert all(r["pdl"] == 0 for r in res)
 
 
 def test_options_from_the_environment_are_range_checked():
