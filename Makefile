@@ -74,7 +74,11 @@ mpirun-link: $(MPI_DEP)
 oracle: $(MPI_DEP) $(BUILD)/libb200p2p.a
 	$(MAKE) -C oracle
 
-tests: $(BUILD)/minimpi_selftest $(BUILD)/driver_unit $(BUILD)/mpi_glue_nogpu
+tests: $(BUILD)/minimpi_selftest $(BUILD)/driver_unit $(BUILD)/mpi_glue_nogpu $(BUILD)/fdpass_unit
+
+$(BUILD)/fdpass_unit: tests/csrc/fdpass_unit.cu $(CSRC)/p2p_internal.h $(BUILD)/libb200p2p.a
+	@mkdir -p $(BUILD)
+	$(NVCC) $(ARCH) -std=c++17 -O1 -Iinclude -I$(CSRC) $< $(BUILD)/libb200p2p.a -o $@
 
 $(BUILD)/mpi_glue_nogpu: tests/csrc/mpi_glue_nogpu.cc include/p2p.h include/p2p_mpi.h $(BUILD)/libb200p2p.a $(MPI_DEP)
 	@mkdir -p $(BUILD)

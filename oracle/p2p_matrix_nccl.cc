@@ -55,6 +55,31 @@ struct NcclBackend {
         NCCLCHECK(ncclGroupEnd());
     }
 
+    // one-to-many the only way the reference's call shape allows it: N-1 sends from the root (p2p_matrix.cc:141-172),
+    // grouped so that they overlap; NCCL_HARNESS_BCAST=collective times ncclBroadcast instead, for context
+    void* symm_alloc(size_t bytes) {
+        void* p = nullptr;
+        CUDACHECK(cudaMalloc(&p, bytes));
+        return p;
+    }
+    void bcast(const void* send, void* recv, size_t bytes, int root, cudaStream_t s) {
+        if (!nranks) NCCLCHECK(ncclCommCount(comm, &nranks));
+        const char* how = getenv("NCCL_HARNESS_BCAST");
+        if (how && !strcmp(how, "collective")) {
+            NCCLCHECK(ncclBroadcast(send, recv, bytes, ncclInt8, root, comm, s));
+            return;
+        }
+        NCCLCHECK(ncclGroupStart());
+        if (rank == root) {
+            for (int p = 0; p < nranks; ++p)
+                if (p != root) NCCLCHECK(ncclSend(send, bytes, ncclInt8, p, comm, s));
+                else CUDACHECK(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
+        } else {
+            NCCLCHECK(ncclRecv(recv, bytes, ncclInt8, root, comm, s));
+        }
+        NCCLCHECK(ncclGroupEnd());
+    }
+
     void fill(void* buf, size_t bytes, uint64_t seed, int r, uint64_t iter, cudaStream_t s) {
         host.resize(bytes);
         oracle_pattern_fill(host.data(), bytes, seed, r, iter);

@@ -4,7 +4,7 @@
 // the exporting process; MPI_Allgather (or any byte transport) cannot carry it.  Each exporting rank therefore
 // listens on an abstract-namespace socket whose name travels in its blob, and hands a duplicate of the descriptor
 // to every peer that asks.  The server is a helper thread that lives from export to import and then ends: the data
-// path has no thread of its own.  Plain host code (no CUDA), unit-tested on CPU by tests/csrc/fdpass_unit.cc.
+// path has no thread of its own.  Plain host code (no CUDA), unit-tested on CPU by tests/csrc/fdpass_unit.cu.
 #include "p2p_internal.h"
 
 #include <algorithm>

@@ -132,7 +132,7 @@ inline void usage(const char* prog, const char* backend) {
            "  --size BYTES[K|M|G]   message size (default 32M)\n"
            "  --iters N             timed iterations per cell (default 128)\n"
            "  --warmup N            untimed iterations per cell (default 0 for --timing ref, 20 for dev)\n"
-           "  --mode M              ref | uni | bidir | allpairs | alltoall | ring | sweep | latency | local\n"
+           "  --mode M              ref | uni | bidir | allpairs | alltoall | bcast | ring | sweep | latency | local\n"
            "  --timing T            ref (rank-0 wall clock, sync per message) | dev (cudaEvents, back to back)\n"
            "  --verify              patterned payload, byte-exact check of every cell's receive buffer\n"
            "  --extra               also print GB/s, us per message and %% of 900 GB/s tables\n"
@@ -195,6 +195,8 @@ inline Options parse_args(int argc, char** argv, int rank, const char* backend) 
 //   void recv(void* buf, size_t bytes, int peer, cudaStream_t s);
 //   void group_start(); void group_end();
 //   void alltoall(const void* send, void* recv, size_t bytes_per_rank, cudaStream_t s);
+//   void* symm_alloc(size_t bytes);                               // collective: memory a broadcast may land in
+//   void bcast(const void* send, void* recv, size_t bytes, int root, cudaStream_t s);
 //   void fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s);
 //   uint64_t check(const void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s,
 //                  uint64_t* digest);                            // mismatching bytes
@@ -490,6 +492,78 @@ public:
             fflush(stdout);
         }
         record("alltoall", -1, -1, bytes, t, flows > 0 ? flows : 1.0);
+    }
+
+    // ---- one-to-many: rank 0's `bytes` into every rank's receive buffer.  The reference can
+    // only write this as N-1 sends from the root (p2p_matrix.cc:141-172 walks the peers one ncclSend at a time); the
+    // NCCL baseline does exactly that, grouped; the engine stores once into the NVSwitch multicast mapping.
+    void run_bcast() {
+        const size_t bytes = o_.size;
+        const int root = 0;
+        uint8_t* dst = (uint8_t*)be_.symm_alloc(bytes + 256);
+        auto round = [&](bool sync) {
+            be_.bcast(send_, dst, bytes, root, s0_);
+            if (sync) CUDACHECK(cudaStreamSynchronize(s0_));
+        };
+        unsigned long long bad_total = 0;
+        if (o_.verify) {
+            for (int rep = 0; rep < 2; ++rep) {   // twice: flags and counters carry over from call to call
+                if (rank_ == root) be_.fill(send_, bytes, o_.seed, root, 99 + (uint64_t)rep, s0_);
+                CUDACHECK(cudaMemsetAsync(dst, 0xA5, bytes + 256, s0_));
+                CUDACHECK(cudaStreamSynchronize(s0_));
+                MPI_Barrier(MPI_COMM_WORLD);
+                round(true);
+                uint64_t digest = 0;
+                unsigned long long b = be_.check(dst, bytes, o_.seed, root, 99 + (uint64_t)rep, s0_, &digest);
+                uint8_t guard[64];
+                CUDACHECK(cudaMemcpy(guard, dst + bytes, sizeof guard, cudaMemcpyDeviceToHost));
+                for (uint8_t gb : guard) if (gb != 0xA5) ++b;
+                unsigned long long total = 0;
+                MPICHECK(MPI_Allreduce(&b, &total, 1, MPI_UINT64_T, MPI_SUM, MPI_COMM_WORLD));
+                bad_total += total;
+                std::vector<unsigned long long> digs((size_t)size_);
+                unsigned long long dg = digest;
+                MPICHECK(MPI_Allgather(&dg, 1, MPI_UINT64_T, digs.data(), 1, MPI_UINT64_T, MPI_COMM_WORLD));
+                if (json_)
+                    for (int r = 0; r < size_; ++r)
+                        fprintf(json_,
+                                "{\"backend\": \"%s\", \"mode\": \"verify\", \"dir\": \"bcast\", \"ranks\": %d, \"src\": %d, \"dst\": %d, "
+                                "\"bytes\": %zu, \"seed\": %llu, \"iter\": %d, \"mismatches\": %llu, \"digest\": \"0x%016llx\"}\n",
+                                be_.name(), size_, root, r, bytes, (unsigned long long)o_.seed, 99 + rep, total, digs[(size_t)r]);
+                MPI_Barrier(MPI_COMM_WORLD);
+            }
+            verified_cells_ += 2 * (uint64_t)size_;
+            verified_bytes_ += 2 * (uint64_t)size_ * bytes;
+            verify_failures_ += bad_total;
+        }
+        for (int i = 0; i < std::max(o_.warmup, 3); ++i) round(true);
+        double t;
+        MPI_Barrier(MPI_COMM_WORLD);
+        if (o_.timing == "dev") {
+            CUDACHECK(cudaEventRecord(ev_[0], s0_));
+            for (int i = 0; i < o_.iters; ++i) round(false);
+            CUDACHECK(cudaEventRecord(ev_[1], s0_));
+            CUDACHECK(cudaStreamSynchronize(s0_));
+            float ms;
+            CUDACHECK(cudaEventElapsedTime(&ms, ev_[0], ev_[1]));
+            double mine = ms * 1e-3 / o_.iters;
+            MPICHECK(MPI_Allreduce(&mine, &t, 1, MPI_DOUBLE, MPI_MAX, MPI_COMM_WORLD));
+        } else {
+            auto start = std::chrono::system_clock::now();
+            for (int i = 0; i < o_.iters; ++i) round(true);
+            MPI_Barrier(MPI_COMM_WORLD);
+            std::chrono::duration<double> el = std::chrono::system_clock::now() - start;
+            t = el.count() / o_.iters;
+            MPICHECK(MPI_Bcast(&t, 1, MPI_DOUBLE, 0, MPI_COMM_WORLD));
+        }
+        const double receivers = (double)std::max(size_ - 1, 1);
+        if (rank_ == 0) {
+            printf("Broadcast from rank %d (%s, timing %s): %d ranks, %zu bytes\n", root, be_.name(), o_.timing.c_str(), size_, bytes);
+            printf("  round %.2f us   %.2f GB/s per receiver   %.2f GB/s delivered in total%s\n", t * 1e6, bytes / t / 1e9,
+                   receivers * bytes / t / 1e9, o_.verify ? (bad_total ? "   VERIFY FAILED" : "   verify OK") : "");
+            fflush(stdout);
+        }
+        record("bcast", root, -1, bytes, t, receivers);
     }
 
     // ---- ring: every rank sends `bytes` to (rank+1)%N and receives from (rank-1)%N at once.
@@ -795,6 +869,7 @@ int run_main(Backend& be, int argc, char** argv) {
     else if (opt.mode == "allpairs") d.run_allpairs();
     else if (opt.mode == "ring") d.run_ring();
     else if (opt.mode == "alltoall") d.run_alltoall();
+    else if (opt.mode == "bcast") d.run_bcast();
     else if (opt.mode == "sweep") d.run_sweep(false);
     else if (opt.mode == "latency") d.run_sweep(true);
     else if (opt.mode == "local") d.run_local();

@@ -32,6 +32,31 @@ struct EngineBackend {
     void group_end() { P2PCHECK(p2p_group_end()); }      // p2p_matrix.cc:227
     void alltoall(const void* send, void* recv, size_t bytes, cudaStream_t s) { P2PCHECK(p2p_alltoall(send, recv, bytes, P2P_INT8, s)); }
 
+    // one-to-many: a symmetric window (driver VMM memory, bound to the NVSwitch multicast object) and p2p_bcast;
+    // P2P_BCAST_SENDS=1 does it the reference's way instead, as N-1 grouped sends from the root, for comparison
+    void* symm_alloc(size_t bytes) {
+        void* p = nullptr;
+        int win = -1;
+        P2PCHECK(p2p_symm_alloc_mpi(MPI_COMM_WORLD, bytes, &p, &win));
+        return p;
+    }
+    void bcast(const void* send, void* recv, size_t bytes, int root, cudaStream_t s) {
+        if (!getenv("P2P_BCAST_SENDS")) {
+            P2PCHECK(p2p_bcast(send, recv, bytes, P2P_INT8, root, s));
+            return;
+        }
+        const int me = p2p_rank(), n = p2p_nranks();
+        P2PCHECK(p2p_group_start());
+        if (me == root) {
+            for (int p = 0; p < n; ++p)
+                if (p != root) P2PCHECK(p2p_send(send, bytes, P2P_INT8, p, s));
+                else CUDACHECK(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
+        } else {
+            P2PCHECK(p2p_recv(recv, bytes, P2P_INT8, root, s));
+        }
+        P2PCHECK(p2p_group_end());
+    }
+
     void fill(void* buf, size_t bytes, uint64_t seed, int rank, uint64_t iter, cudaStream_t s) {
         P2PCHECK(p2p_pattern_fill(buf, bytes, seed, rank, iter, s));
     }

@@ -36,7 +36,7 @@ def built():
     needed = [os.path.join(ROOT, "test-nccl-p2p_b200", "lib", "libb200p2p.so"), P2P_MATRIX, MPIRUN,
               os.path.join(REF_DIR, "libp2poracle.so"), os.path.join(REF_DIR, "mpi_host_p2p"),
               os.path.join(ROOT, "build", "minimpi_selftest"), os.path.join(ROOT, "build", "driver_unit"),
-              os.path.join(ROOT, "build", "mpi_glue_nogpu")]
+              os.path.join(ROOT, "build", "mpi_glue_nogpu"), os.path.join(ROOT, "build", "fdpass_unit")]
     if not all(_have(p) for p in needed):
         sys.path.insert(0, ROOT)
         entry = importlib.import_module("__graft_entry__")
