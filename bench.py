@@ -208,6 +208,9 @@ def nccl_side_numbers(n: int, allpairs_bytes: int):
     recs, log = matrix_run(exe, n, ["--mode", "allpairs", "--size", str(allpairs_bytes), "--iters", "30", "--warmup", "3", "--timing", "dev"])
     ap = [r for r in (recs or []) if r["mode"] == "allpairs"]
     out["nccl_allpairs_aggregate_GBps"] = round(ap[0]["GBps"], 2) if ap else None
+    recs, log = matrix_run(exe, n, ["--mode", "bcast", "--size", str(allpairs_bytes), "--iters", "30", "--warmup", "3", "--timing", "dev"])
+    bc = [r for r in (recs or []) if r["mode"] == "bcast"]
+    out["nccl_bcast_grouped_sends_64MiB_GBps_per_receiver"] = round(bc[0]["GBps"] / max(n - 1, 1), 2) if bc else None
     recs, log = matrix_run(exe, n, ["--mode", "latency", "--sweep-min", "8", "--sweep-max", "8", "--iters", "2000"])
     lat = [r for r in (recs or []) if r["mode"] == "latency" and r["bytes"] == 8]
     out["nccl_latency_8B_oneway_us"] = round(lat[0]["us"], 3) if lat else None
@@ -531,6 +534,19 @@ def side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max
     out["allpairs_bytes_per_flow"] = n
     out["allpairs_aggregate_GBps"] = round(world * (world - 1) * n / (t / 30) / 1e9, 2)
     p2p.raise_async_error()
+
+    # one-to-many: rank 0's 64 MiB into every rank's buffer through the NVSwitch multicast mapping
+    try:
+        sym = p2p.SymmBuffer(n + 256, gather)
+        def bcast():
+            p2p.bcast(src.ptr, sym.ptr, n, p2p.INT8, 0, stream)
+        events_around(bcast, 3)
+        t = events_around(bcast, 30)
+        out["bcast_64MiB_GBps_per_receiver"] = round(n / (t / 30) / 1e9, 2)
+        out["bcast_multicast"] = bool(sym.multicast_ptr)
+        p2p.raise_async_error()
+    except p2p.P2PError as e:
+        out["bcast_unavailable"] = str(e)[:200]
     return out
 
 

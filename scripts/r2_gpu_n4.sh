@@ -10,7 +10,13 @@ run() { local name=$1 t=$2; shift 2; timeout $t "$@" > $OUT/$name.log 2>&1; echo
 
 run pytest_multi 900 python -m pytest tests/test_symm.py tests/test_gpu_multi.py -m gpu -x -q -p timeout --timeout 300
 
-last() { tail -n ${2:-2} $1; }
+# the lane-based staging ring (receive buffers in no window): parity on one GPU, rate on one pair
+run pytest_staging 600 python -m pytest tests/test_gpu_self.py -m gpu -x -q -k "staging or pdl_modes or pull_path" -p timeout --timeout 300
+for e in "P2P_NO_WINDOWS=1" "P2P_NO_WINDOWS=1 P2P_STAGE_CHUNK=131072" "P2P_NO_WINDOWS=1 P2P_STAGE_CHUNK=524288" "P2P_NO_WINDOWS=1 P2P_STAGE_LANES=8" "P2P_NO_RECV_WINDOW=1"; do
+  name=$(echo "$e" | tr ' =' '__')
+  env $e timeout 200 $MPI -n 2 ./p2p_matrix --mode sweep --sweep-min 1M --sweep-max 256M --iters 50 --verify --json $OUT/sweep_$name.json > $OUT/sweep_$name.log 2>&1; echo "exit $?" >> $OUT/sweep_$name.log
+done
+timeout 200 $MPI -n 2 $REF/p2p_matrix_nccl --mode sweep --sweep-min 1M --sweep-max 256M --iters 50 --json $OUT/sweep_nccl_n2.json > $OUT/sweep_nccl_n2.log 2>&1
 # ---- ring step (bench.py's step): who moves the bytes when a GPU sends and receives at once
 : > $OUT/ring.log
 rng() { echo "== $*" >> $OUT/ring.log; for sz in 67108864 268435456; do env "$@" timeout 100 $MPI -n $N ./p2p_matrix --mode ring --size $sz --iters 40 --warmup 5 --timing dev --verify 2>&1 | tail -2 >> $OUT/ring.log; done; }
@@ -73,5 +79,6 @@ run bench_engine 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node
 
 tail -n 4 $OUT/pytest_multi.log
 cat $OUT/ring.log $OUT/allpairs.log $OUT/alltoall.log $OUT/bcast.log
-for f in $OUT/sweep_engine.log $OUT/sweep_nccl.log; do echo "== $f"; grep -E "^ +[0-9]+ " $f | awk '{print $1, $2, $3, $4}' | tr '\n' ';'; echo; grep -h "verify" $f | tail -1; done
+tail -n 3 $OUT/pytest_staging.log
+for f in $OUT/sweep_*.log; do echo "== $f"; grep -E "^ +[0-9]+ " $f | awk '{print $1, $2, $3, $4}' | tr '\n' ';'; echo; grep -h "verify" $f | tail -1; done
 grep -h '"metric"' $OUT/bench_*.log | cut -c1-3000

@@ -67,23 +67,32 @@ struct alignas(8) OpDesc {
 };
 
 // Staging ring between one ordered pair of ranks, for receive buffers that are in no window (plain cudaMalloc
-// memory nobody registered, as in the reference, p2p_matrix.cc:127-128): the sender stores chunk c into slot
-// c % slots of a ring in the RECEIVER's control region and publishes `filled`, the receiver copies the chunk out
-// into its buffer and publishes `drained` at the sender.  Both counters are (seq << 24 | chunks), so they never
-// need resetting.  One such message per ordered pair at a time (`lock`, taken by the receiver before it asks).
-struct StageInfo {
-    uint64_t send_ring;     // peer-mapped: the ring in the peer's region that my sends to it go through
-    uint64_t send_filled;   // peer-mapped flag I publish after each chunk
-    uint64_t send_drained;  // local flag the peer publishes when it has copied a chunk out
-    uint64_t send_arrive;   // local u32[slots]: CTAs of the send that have finished the chunk in that slot
-    uint64_t recv_ring;     // local: the ring my receives from this peer come through
-    uint64_t recv_filled;   // local
-    uint64_t recv_drained;  // peer-mapped
-    uint64_t recv_arrive;   // local u32[slots]
-    uint64_t lock;          // local u32
-    uint32_t chunk, slots;
-};
+// memory nobody registered, as in the reference, p2p_matrix.cc:127-128).  The message is cut into chunks; chunk c
+// belongs to lane c % lanes, and each lane is a private ring of `slots` chunk-sized slots in the RECEIVER's control
+// region with its own pair of counters: the sender stores the chunk into the lane's next slot and publishes
+// `filled[lane]`, the receiver copies it out into its buffer and publishes `drained[lane]` at the sender.  A lane
+// is served by one CTA on each side, so no chunk needs a barrier between CTAs: the lanes stream independently.
+// Counters are (seq << 24 | chunks of this lane), so they never need resetting.  One such message per ordered pair
+// at a time (`lock`, taken by the receiver before it asks).
+constexpr int kStageLanes = 16;
 constexpr int kStageSlots = 4;
+struct StageHeader {                  // first 4 KiB of the ring area [region of rank r][from rank q]
+    uint64_t filled[kStageLanes];     // q -> r traffic: chunks q has stored into each lane   (written by q)
+    uint64_t drained[kStageLanes];    // r -> q traffic: chunks q has copied out of each lane (written by q)
+};
+constexpr size_t kStageHeaderBytes = 4096;
+struct StageInfo {
+    uint64_t send_ring;     // peer-mapped: lane 0, slot 0 of the ring in the peer's region that my sends to it go through
+    uint64_t send_filled;   // peer-mapped u64[lanes] I publish into
+    uint64_t send_drained;  // local u64[lanes] the peer publishes into
+    uint64_t send_arrive;   // local u32: CTAs of the send that are through with all their chunks
+    uint64_t recv_ring;     // local
+    uint64_t recv_filled;   // local u64[lanes]
+    uint64_t recv_drained;  // peer-mapped u64[lanes]
+    uint64_t recv_arrive;   // local u32
+    uint64_t lock;          // local u32
+    uint32_t chunk, slots, lanes, pad;
+};
 __host__ __device__ __forceinline__ uint64_t stage_count(uint64_t seq, uint64_t chunks) { return (seq << 24) | chunks; }
 
 enum OpFlags : uint32_t {
@@ -556,23 +565,39 @@ struct CopyJob {
     uint32_t part;
     bool is_push;        // destination is peer memory (the TMA flavour stages these)
     uint32_t staged;     // 0 direct, 1 sending through the staging ring, 2 receiving through it
-    uint32_t chunk;      // staged: index of the chunk this pass moves
+    uint32_t chunk;      // staged: index of the chunk this pass moves (== nchunks: this CTA has none left)
+    uint32_t nchunks;
 };
 
-// Staged message, before a chunk is copied: wait until its ring slot may be written (send: the receiver has
-// drained the chunk that used it before) or read (receive: the sender has filled it); point the job at it.
+// Which chunks a CTA of a staged message serves: lane l belongs to CTA l % nblocks (on either side, whatever the
+// two sides' CTA counts are), a CTA walks its chunks in increasing order.  Returns nchunks when there is none left.
+__device__ __forceinline__ uint32_t stage_next_chunk(uint32_t from, uint32_t nchunks, uint32_t lanes, uint32_t part, uint32_t nblocks) {
+    for (uint32_t c = from; c < nchunks; ++c)
+        if ((c % lanes) % nblocks == part) return c;
+    return nchunks;
+}
+
+// Staged message, first of all: how many chunks there are and which one this CTA starts with.
+__device__ __forceinline__ void stage_start(CopyJob& job) {
+    const StageInfo* st = (const StageInfo*)job.op->stage;
+    job.nchunks = (uint32_t)((job.op->nbytes + st->chunk - 1) / st->chunk);
+    job.chunk = stage_next_chunk(0, job.nchunks, st->lanes, job.part, job.op->nblocks);
+}
+
+// Staged message, before a chunk is copied: wait until its slot may be written (send: the receiver has drained the
+// chunk that used it before) or read (receive: the sender has filled it); point the job at it.
 __device__ __forceinline__ bool stage_begin(const GroupHdr& h, CopyJob& job, uint64_t* smem_slot) {
     const OpDesc& op = *job.op;
     const StageInfo* st = (const StageInfo*)op.stage;
-    const uint32_t c = job.chunk;
+    const uint32_t c = job.chunk, lane = c % st->lanes, k = c / st->lanes;
     const bool send = job.staged == 1;
     __syncthreads();  // smem_slot is reused from pass to pass
     if (threadIdx.x == 0) {
         uint64_t ok = 1, v;
-        const uint64_t want = send ? stage_count(op.seq, c + 1 - st->slots) : stage_count(op.seq, c + 1);
-        if (!send || c >= st->slots) {
-            const uint64_t* flag = (const uint64_t*)(send ? st->send_drained : st->recv_filled);
-            // counts of this very message only: an older message's count has a smaller sequence number
+        if (!send || k >= st->slots) {
+            // counts of this very message only: an older message's count carries a smaller sequence number
+            const uint64_t want = send ? stage_count(op.seq, k + 1 - st->slots) : stage_count(op.seq, k + 1);
+            const uint64_t* flag = (const uint64_t*)(send ? st->send_drained : st->recv_filled) + lane;
             if (!spin_flag(flag, h.timeout_ns, v, [want](uint64_t x) { return x >= want; })) {
                 report_error(h, AERR_TIMEOUT_STAGE);
                 ok = 0;
@@ -585,34 +610,42 @@ __device__ __forceinline__ bool stage_begin(const GroupHdr& h, CopyJob& job, uin
     const size_t off = (size_t)c * st->chunk;
     job.nbytes = op.nbytes - off < st->chunk ? op.nbytes - off : st->chunk;
     uint8_t* user = (uint8_t*)op.local + off;
-    uint8_t* slot = (uint8_t*)(send ? st->send_ring : st->recv_ring) + (size_t)(c % st->slots) * st->chunk;
+    uint8_t* slot = (uint8_t*)(send ? st->send_ring : st->recv_ring) + ((size_t)lane * st->slots + k % st->slots) * st->chunk;
     job.dst = send ? slot : user;
     job.src = send ? user : slot;
     return true;
 }
 
-// After the chunk: the last CTA of the op to finish it publishes the count.  Returns true while chunks remain.
+// After the chunk: publish the lane's count.  After a CTA's last chunk: the last CTA of the op to get there zeroes
+// the consumed post slot and (receiver) frees the pair's ring.  Returns true while this CTA has chunks left.
 __device__ __forceinline__ bool stage_end(const GroupHdr& h, CopyJob& job) {
     const OpDesc& op = *job.op;
     const StageInfo* st = (const StageInfo*)op.stage;
-    const uint32_t c = job.chunk;
     const bool send = job.staged == 1;
-    const uint32_t nchunks = (uint32_t)((op.nbytes + st->chunk - 1) / st->chunk);
-    const bool last_chunk = c + 1 == nchunks;
-    __syncthreads();
-    if (last_chunk) pdl_trigger_late(h);
+    const uint32_t nchunks = job.nchunks;
+    const uint32_t c = job.chunk;
+    const uint32_t next = c < nchunks ? stage_next_chunk(c + 1, nchunks, st->lanes, job.part, op.nblocks) : nchunks;
+    __syncthreads();  // every thread's accesses to the slot are issued (receive: its loads have returned)
+    if (next >= nchunks) pdl_trigger_late(h);
     if (threadIdx.x == 0) {
-        fence_sys();
-        uint32_t* arrive = (uint32_t*)(send ? st->send_arrive : st->recv_arrive) + (c % st->slots);
-        const uint32_t old = atomicInc(arrive, op.nblocks - 1);
-        if (old == op.nblocks - 1) {
-            if (last_chunk && job.consumed) *(volatile uint64_t*)job.consumed = 0;
-            st_release_sys((uint64_t*)(send ? st->send_filled : st->recv_drained), stage_count(op.seq, c + 1));
-            if (last_chunk && !send) atomicExch((uint32_t*)st->lock, 0u);  // the pair's ring is free again
+        if (c < nchunks) {
+            const uint32_t lane = c % st->lanes, k = c / st->lanes;
+            if (send) st_release_sys((uint64_t*)st->send_filled + lane, stage_count(op.seq, k + 1));
+            else st_relaxed_sys((uint64_t*)st->recv_drained + lane, stage_count(op.seq, k + 1));  // loads are done: no fence needed
+        }
+        if (next >= nchunks) {
+            const uint32_t old = atomicInc((uint32_t*)(send ? st->send_arrive : st->recv_arrive), op.nblocks - 1);
+            if (old == op.nblocks - 1) {
+                if (job.consumed) *(volatile uint64_t*)job.consumed = 0;
+                if (!send) {
+                    __threadfence();
+                    atomicExch((uint32_t*)st->lock, 0u);  // the pair's ring is free again
+                }
+            }
         }
     }
-    job.chunk = c + 1;
-    return !last_chunk;
+    job.chunk = next;
+    return next < nchunks;
 }
 
 // Runs the control / eager roles to completion and resolves the mover roles to a CopyJob, so
@@ -631,6 +664,7 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
     job.nbytes = op->nbytes;
     job.staged = 0;
     job.chunk = 0;
+    job.nchunks = 0;
     switch (op->kind) {
         case OP_PUSH:
             job.dst = push_wait_post(h, *op, part, slot);

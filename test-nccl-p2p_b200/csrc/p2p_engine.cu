@@ -41,6 +41,7 @@ struct BootBlob {
     char pci_bus_id[32];
     char hostbox_name[48];  // rank 0 only: POSIX shared-memory name of the host mailbox
     cudaIpcMemHandle_t ctl_handle;
+    uint32_t stage_chunk, stage_lanes;  // shape of the staging ring, which both ends of a pair walk
 };
 static_assert(sizeof(BootBlob) <= kBlobBytes, "bootstrap blob too large");
 
@@ -65,9 +66,7 @@ struct PeerCtl {
     uint64_t pull_post[kRing];
     uint64_t pull_done[kRing];
     uint64_t ll_ack[kLLSlots];
-    uint64_t stage_filled;   // written by the peer as sender through my staging ring: (seq << 24 | chunks filled)
-    uint64_t stage_drained;  // written by the peer as receiver of my staged sends: (seq << 24 | chunks copied out)
-    uint64_t pad[6];
+    uint64_t pad[8];
 };
 
 // Host mailbox (POSIX shared memory, one per job): the receiver's HOST publishes where a large receive goes at the
@@ -135,7 +134,9 @@ struct Options {
                                    // it loses to the pull kernel (256 MiB: 708 vs 726 GB/s streamed, 496 vs 368 us per
                                    // ping-pong hop): kernel -> DMA -> kernel on one stream costs more than the DMA gains.
     long long ce_wait_us = 200;    // how long p2p_send's host side waits for that word before using the SM path
-    long long stage_chunk = 1 << 20;  // bytes per slot of the staging ring (receive buffers that are in no window); same on all ranks
+    long long stage_chunk = 256 << 10;  // bytes per slot of the staging ring's lanes (receive buffers that are in no window): 16 lanes
+                                        // x 4 slots x this per ordered pair of ranks; same on all ranks
+    long long stage_lanes = kStageLanes;
     long long ce_flags = 1;        // who handles the flags around the DMA: 0 two one-thread kernels (round 1), 1 stream memory
                                    // operations (cuStreamWaitValue64 / cuStreamWriteValue64: nothing to launch, so the chain
                                    // may run beside a group's kernel), 2 as 1 but flags in PEER memory are written by 8-byte DMA
@@ -309,6 +310,7 @@ const OptionSpec kOptionSpecs[] = {
     {"ce_wait_us", "P2P_CE_WAIT_US", &Options::ce_wait_us, 0, 10000000},
     {"ce_flags", "P2P_CE_FLAGS", &Options::ce_flags, 0, 2},
     {"stage_chunk", "P2P_STAGE_CHUNK", &Options::stage_chunk, 4096, 16 << 20},
+    {"stage_lanes", "P2P_STAGE_LANES", &Options::stage_lanes, 1, kStageLanes},
 };
 
 const OptionSpec* find_option(const char* name) {
@@ -490,28 +492,30 @@ bool lookup_window(const void* buf, size_t nbytes, uint32_t* win, uint64_t* off)
 inline uint32_t* arrive_push(int p, uint64_t seq) { return g.arrive + (size_t)p * kRing + seq % kRing; }
 inline uint32_t* arrive_pull(int p, uint64_t seq) { return g.arrive + (size_t)(g.nranks + p) * kRing + seq % kRing; }
 inline uint32_t* arrive_ll(int p, uint64_t seq) { return g.arrive + (size_t)2 * g.nranks * kRing + (size_t)p * kLLSlots + seq % kLLSlots; }
-// staging ring: per peer kStageSlots send counters, kStageSlots receive counters, one lock
-inline size_t arrive_words(int nranks) { return (size_t)nranks * (2 * kRing + kLLSlots + 2 * kStageSlots + 1); }
-inline uint32_t* arrive_stage(int p) { return g.arrive + (size_t)g.nranks * (2 * kRing + kLLSlots) + (size_t)p * (2 * kStageSlots + 1); }
-inline uint8_t* stage_ring(uint8_t* region, int from) { return region + g.stage_off + (size_t)from * kStageSlots * (size_t)g.opt.stage_chunk; }
+// staging ring: per peer one send counter, one receive counter, one lock
+inline size_t arrive_words(int nranks) { return (size_t)nranks * (2 * kRing + kLLSlots + 3); }
+inline uint32_t* arrive_stage(int p) { return g.arrive + (size_t)g.nranks * (2 * kRing + kLLSlots) + (size_t)p * 3; }
+inline size_t stage_area_bytes() { return kStageHeaderBytes + (size_t)kStageLanes * kStageSlots * (size_t)g.opt.stage_chunk; }
+inline uint8_t* stage_area(uint8_t* region, int from) { return region + g.stage_off + (size_t)from * stage_area_bytes(); }
 
 // Where everything of the staging ring between me and peer p lies, as the kernels need it.
 StageInfo stage_info_for(int p) {
     StageInfo si;
     memset(&si, 0, sizeof si);
-    uint8_t* my = g.ctl;
-    uint8_t* theirs = g.peer_ctl[p];
-    si.send_ring = (uint64_t)stage_ring(theirs, g.rank);
-    si.send_filled = (uint64_t)&peer_section(theirs, g.rank)->stage_filled;
-    si.send_drained = (uint64_t)&peer_section(my, p)->stage_drained;
+    StageHeader* mine = (StageHeader*)stage_area(g.ctl, p);               // in my region: what p writes
+    StageHeader* theirs = (StageHeader*)stage_area(g.peer_ctl[p], g.rank);  // in p's region: what I write
+    si.send_ring = (uint64_t)((uint8_t*)theirs + kStageHeaderBytes);
+    si.send_filled = (uint64_t)theirs->filled;
+    si.send_drained = (uint64_t)mine->drained;
     si.send_arrive = (uint64_t)arrive_stage(p);
-    si.recv_ring = (uint64_t)stage_ring(my, p);
-    si.recv_filled = (uint64_t)&peer_section(my, p)->stage_filled;
-    si.recv_drained = (uint64_t)&peer_section(theirs, g.rank)->stage_drained;
-    si.recv_arrive = (uint64_t)(arrive_stage(p) + kStageSlots);
-    si.lock = (uint64_t)(arrive_stage(p) + 2 * kStageSlots);
+    si.recv_ring = (uint64_t)((uint8_t*)mine + kStageHeaderBytes);
+    si.recv_filled = (uint64_t)mine->filled;
+    si.recv_drained = (uint64_t)theirs->drained;
+    si.recv_arrive = (uint64_t)(arrive_stage(p) + 1);
+    si.lock = (uint64_t)(arrive_stage(p) + 2);
     si.chunk = (uint32_t)g.opt.stage_chunk;
     si.slots = kStageSlots;
+    si.lanes = (uint32_t)g.opt.stage_lanes;
     return si;
 }
 
@@ -711,7 +715,7 @@ void size_roles(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, G
             case PROTO_PUSH:
                 shape.only_small = false;
                 if (op.is_send) { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false, 1, shape.tma_chunk); want += r.nblocks; }
-                else if (r.staged) { r.nblocks = std::min(16, mover_ctas(op.nbytes, FLAVOUR_LDST, self, true)); want += r.nblocks; }
+                else if (r.staged) { r.nblocks = std::min<int>(kStageLanes, mover_ctas(op.nbytes, FLAVOUR_LDST, self, true)); want += r.nblocks; }
                 else ++shape.n_ctrl;
                 break;
             case PROTO_LARGE:
@@ -1198,7 +1202,7 @@ int p2p_init(int rank, int nranks, int device) {
     g.ll_slot_bytes = (g.ll_slot_bytes + 255) & ~(size_t)255;
     g.ll_off = (sizeof(PeerCtl) * (size_t)nranks + 4095) & ~(size_t)4095;
     g.stage_off = (g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes + 4095) & ~(size_t)4095;
-    g.ctl_bytes = g.stage_off + (size_t)nranks * kStageSlots * (size_t)o.stage_chunk;
+    g.ctl_bytes = g.stage_off + (size_t)nranks * stage_area_bytes();
     CUDA_TRY(cudaMalloc(&g.ctl, g.ctl_bytes));
     CUDA_TRY(cudaMemset(g.ctl, 0, g.ctl_bytes));
     CUDA_TRY(cudaMalloc(&g.arrive, sizeof(uint32_t) * arrive_words(nranks)));
@@ -1264,6 +1268,8 @@ int p2p_export(void* blob) {
     b.eager_bytes = (uint64_t)g.opt.eager_bytes;
     b.pull_min_bytes = g.opt.pull_min_bytes;
     b.ctl_bytes = g.ctl_bytes;
+    b.stage_chunk = (uint32_t)g.opt.stage_chunk;
+    b.stage_lanes = (uint32_t)g.opt.stage_lanes;
     CUDA_TRY(cudaDeviceGetPCIBusId(b.pci_bus_id, sizeof b.pci_bus_id, g.device));
     memcpy(b.hostbox_name, g.hostbox_name, sizeof b.hostbox_name);
     if (g.nranks > 1) CUDA_TRY(cudaIpcGetMemHandle(&b.ctl_handle, g.ctl));
@@ -1289,6 +1295,9 @@ int p2p_connect(const void* all_blobs) {
         if (b.eager_bytes != (uint64_t)g.opt.eager_bytes)
             return fail(P2P_INVALID_USAGE, "rank %d uses eager_bytes=%llu, this rank %lld; they must match", r,
                         (unsigned long long)b.eager_bytes, g.opt.eager_bytes);
+        if (b.stage_chunk != (uint32_t)g.opt.stage_chunk || b.stage_lanes != (uint32_t)g.opt.stage_lanes)
+            return fail(P2P_INVALID_USAGE, "rank %d uses a staging ring of %u lanes x %u bytes, this rank %lld x %lld; they must match", r,
+                        b.stage_lanes, b.stage_chunk, g.opt.stage_lanes, g.opt.stage_chunk);
         if (b.pull_min_bytes != g.opt.pull_min_bytes)
             return fail(P2P_INVALID_USAGE, "rank %d uses pull_min_bytes=%lld, this rank %lld; they must match", r,
                         (long long)b.pull_min_bytes, g.opt.pull_min_bytes);
@@ -1634,8 +1643,8 @@ int p2p_set_option(const char* name, long long value) {
     if (!sp) return fail(P2P_INVALID_ARGUMENT, "unknown option '%s'", name);
     if (!strcmp(name, "pull_min_bytes"))
         return fail(P2P_INVALID_USAGE, "pull_min_bytes is agreed between ranks at p2p_connect; set P2P_PULL_MIN_BYTES before p2p_init");
-    if (!strcmp(name, "stage_chunk"))
-        return fail(P2P_INVALID_USAGE, "stage_chunk sizes the control region; set P2P_STAGE_CHUNK before p2p_init (same on all ranks)");
+    if (!strcmp(name, "stage_chunk") || !strcmp(name, "stage_lanes"))
+        return fail(P2P_INVALID_USAGE, "%s shapes the staging ring both ends share; set P2P_STAGE_CHUNK / P2P_STAGE_LANES before p2p_init (same on all ranks)", name);
     int rc = validate_option(*sp, value, g.opt, "");
     if (rc) return rc;
     // the rings were sized in p2p_init; the limit can only shrink afterwards, and on every rank alike
@@ -1745,7 +1754,7 @@ int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int c
     g.ll_slot_bytes = ((size_t)std::max<long long>(o.eager_bytes, 8) * 2 + 255) & ~(size_t)255;
     g.ll_off = (sizeof(PeerCtl) * (size_t)nranks + 4095) & ~(size_t)4095;
     g.stage_off = (g.ll_off + (size_t)nranks * kLLSlots * g.ll_slot_bytes + 4095) & ~(size_t)4095;
-    g.ctl_bytes = g.stage_off + (size_t)nranks * kStageSlots * (size_t)o.stage_chunk;
+    g.ctl_bytes = g.stage_off + (size_t)nranks * stage_area_bytes();
     g.stage_table = (StageInfo*)0x500000000000ull;
     for (int r = 0; r < nranks; ++r) g.peer_ctl[r] = (uint8_t*)(0x100000000000ull + (uint64_t)r * 0x1000000000ull);
     g.ctl = g.peer_ctl[rank];

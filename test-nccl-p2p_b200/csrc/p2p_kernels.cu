@@ -15,9 +15,11 @@ p2p_group_kernel_ldst(const __grid_constant__ GroupArgsT<MAXOPS> a) {
     __shared__ uint64_t slot;
     CopyJob job;
     if (!resolve_role(a.h, a.ops, &slot, job)) return;
-    for (;;) {  // one pass, or one per chunk of a message that goes through the staging ring
-        if (job.staged && !stage_begin(a.h, job, &slot)) return;
-        copy_bytes(job.dst, job.src, job.nbytes, job.part, job.op->nblocks);
+    if (job.staged) stage_start(job);
+    for (;;) {  // one pass - or, for a message that goes through the staging ring, one per chunk of this CTA's lanes
+        const bool idle = job.staged && job.chunk >= job.nchunks;   // more CTAs than lanes, or a short message
+        if (job.staged && !idle && !stage_begin(a.h, job, &slot)) return;
+        if (!idle) copy_bytes(job.dst, job.src, job.nbytes, job.staged ? 0 : job.part, job.staged ? 1 : job.op->nblocks);
         if (!job.staged || !stage_end(a.h, job)) break;
     }
     if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);
@@ -42,12 +44,14 @@ p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
     if (!resolve_role(a.h, a.ops, &slot, job)) return;
     // the ring moves pushes, pulls and local copies whose two sides share their 16-byte phase; anything else, and
     // the chunks of a message that goes through the staging ring, keep the register loop
+    if (job.staged) stage_start(job);
     for (;;) {
-        if (job.staged && !stage_begin(a.h, job, &slot)) return;
+        const bool idle = job.staged && job.chunk >= job.nchunks;
+        if (job.staged && !idle && !stage_begin(a.h, job, &slot)) return;
         if (!job.staged && (((uint64_t)job.dst ^ (uint64_t)job.src) & 15) == 0)
             tma_push(job.dst, job.src, job.nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty);
-        else
-            copy_bytes(job.dst, job.src, job.nbytes, job.part, job.op->nblocks);
+        else if (!idle)
+            copy_bytes(job.dst, job.src, job.nbytes, job.staged ? 0 : job.part, job.staged ? 1 : job.op->nblocks);
         if (!job.staged || !stage_end(a.h, job)) break;
     }
     if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);

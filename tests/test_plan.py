@@ -252,10 +252,12 @@ hh, cb = ctypes.c_uint64(), ctypes.c_size_t()
 assert L.p2p_debug_plan_disconnect(ctypes.byref(hh), ctypes.byref(cb)) == 0
 n = L.p2p_blob_bytes()
 
-def blob(rank, host_hash=hh.value, eager=p2p.get_option("eager_bytes"), pull=p2p.get_option("pull_min_bytes"), magic=0x42325032, nranks=2, bus=None):
+def blob(rank, host_hash=hh.value, eager=p2p.get_option("eager_bytes"), pull=p2p.get_option("pull_min_bytes"), magic=0x42325032, nranks=2, bus=None, stage_chunk=256 << 10):
     # BootBlob: magic, version, rank, nranks, host_hash, pid, device, eager_bytes, pull_min_bytes, ctl_bytes, pci_bus_id[32], ...
     head = struct.pack("<IIiiQiiQqQ", magic, 1, rank, nranks, host_hash, 424242 + rank, rank, eager, pull, cb.value)
     head += (bus if bus is not None else ("0000:%%02x:00.0" %% (rank + 1))).encode().ljust(32, b"\0")
+    head += bytes(48 + 64)                                   # hostbox_name, ctl_handle
+    head += struct.pack("<II", stage_chunk, 16)              # stage_chunk, stage_lanes
     return head + bytes(n - len(head))
 
 def connect(b0, b1):
@@ -268,6 +270,8 @@ rc, why = connect(blob(0), blob(1, eager=12345))
 assert rc == p2p.INVALID_USAGE and "eager_bytes" in why, (rc, why)
 rc, why = connect(blob(0), blob(1, pull=1 << 30))
 assert rc == p2p.INVALID_USAGE and "pull_min_bytes" in why, (rc, why)
+rc, why = connect(blob(0), blob(1, stage_chunk=1 << 20))
+assert rc == p2p.INVALID_USAGE and "staging ring" in why, (rc, why)
 rc, why = connect(blob(1), blob(0))
 assert rc == p2p.INVALID_ARGUMENT and "rank order" in why, (rc, why)
 rc, why = connect(blob(0), blob(1, magic=7))

@@ -31,57 +31,89 @@ WINDOWS = [[SEND_WIN, 1 << 30], [RECV_WIN, 4 << 30]]
 VALID, OFFMASK, PUSH_PLEASE, STAGED = 1 << 39, (1 << 39) - 1, 0xFF, 0xFE
 CTL_BASE, CTL_STRIDE = 0x100000000000, 0x1000000000
 SECTION = (64 * 4 + 4 + 8) * 8            # sizeof(PeerCtl)
-STAGE_FILLED, STAGE_DRAINED = 2080, 2088  # offsets in PeerCtl, after post/done/pull_post/pull_done[64] and ll_ack[4]
-STAGE_CHUNK, STAGE_SLOTS = 1 << 20, 4
+STAGE_CHUNK, STAGE_SLOTS, STAGE_LANES = 256 << 10, 4, 16
+MiB = 1 << 20
+CLEAR_CONSUMED_SLOTS = True   # what the device code does; the wrap test below also shows what happens without
 
 
-def ctl_flag(region_rank, section_peer, offset):
-    return CTL_BASE + region_rank * CTL_STRIDE + section_peer * SECTION + offset
+def stage_flag(region_rank, from_rank, kind, lane):
+    """Counter `kind`[lane] in the header of the ring area [region of region_rank][from from_rank] (written by from_rank)."""
+    return ("stage", region_rank, from_rank, kind, lane)
 
 
 def stage_count(seq, chunks):
     return (seq << 24) | chunks
 
 
+def stage_chunks_of(cta, nctas, nchunks):
+    """Chunks a CTA of a staged message serves: lane l belongs to CTA l % nctas; increasing order."""
+    return [c for c in range(nchunks) if (c % STAGE_LANES) % nctas == cta]
+
+
+def interleave(world, ctas):
+    """Several CTAs of one role: each step one of those that still run advances, chosen at random."""
+    ctas = list(ctas)
+    while ctas:
+        g = world.rng.choice(ctas)
+        try:
+            next(g)
+        except StopIteration:
+            ctas.remove(g)
+        yield
+
+
 def staged_send(world, src, dst, op):
-    """Sender side of the staging ring (stage_begin / stage_end of csrc/p2p_device.cuh, chunk by chunk)."""
-    seq, n = op["seq"], op["nbytes"]
-    drained, filled = ctl_flag(src, dst, STAGE_DRAINED), ctl_flag(dst, src, STAGE_FILLED)
+    """Sender side of the staging ring (stage_begin / stage_end of csrc/p2p_device.cuh), CTA by CTA, chunk by chunk."""
+    seq, n, nctas = op["seq"], op["nbytes"], max(op["nblocks"], 1)
     nchunks = -(-n // STAGE_CHUNK)
-    for c in range(nchunks):
-        if c >= STAGE_SLOTS:
-            while world.flags.get(drained, 0) < stage_count(seq, c + 1 - STAGE_SLOTS):
-                yield
-        world.ring[("stage", src, dst, c % STAGE_SLOTS)] = (seq, c, op["local"])
-        if c + 1 == nchunks and CLEAR_CONSUMED_SLOTS:
+    done = [0]
+
+    def cta(j):
+        for c in stage_chunks_of(j, nctas, nchunks):
+            lane, k = c % STAGE_LANES, c // STAGE_LANES
+            if k >= STAGE_SLOTS:
+                while world.flags.get(stage_flag(src, dst, "drained", lane), 0) < stage_count(seq, k + 1 - STAGE_SLOTS):
+                    yield
+            world.ring[("stage", src, dst, lane, k % STAGE_SLOTS)] = (seq, c, op["local"])
+            world.flags[stage_flag(dst, src, "filled", lane)] = stage_count(seq, k + 1)
+            yield
+        done[0] += 1
+        if done[0] == nctas and CLEAR_CONSUMED_SLOTS:
             world.flags[op["f_wait"]] = 0
-        world.flags[filled] = stage_count(seq, c + 1)
+
+    yield from interleave(world, [cta(j) for j in range(nctas)])
 
 
 def staged_recv(world, dst, src, op, consumed=None):
-    """Receiver side: take the pair's ring, ask the sender to use it, copy chunk after chunk out."""
-    seq, n = op["seq"], op["nbytes"]
+    """Receiver side: take the pair's ring, ask the sender to use it, copy chunk after chunk out of its lanes."""
+    seq, n, nctas = op["seq"], op["nbytes"], max(op["nblocks"], 1)
     lock = ("stage_lock", dst, src)
     while world.flags.get(lock, 0):
         yield
     world.flags[lock] = 1
     world.flags[op["f_signal"]] = (seq & 0xFFFF) << 48 | STAGED << 40 | VALID
-    drained, filled = ctl_flag(src, dst, STAGE_DRAINED), ctl_flag(dst, src, STAGE_FILLED)
     nchunks = -(-n // STAGE_CHUNK)
-    source = None
-    for c in range(nchunks):
-        while world.flags.get(filled, 0) < stage_count(seq, c + 1):
+    got_chunks, done = {}, [0]
+
+    def cta(j):
+        for c in stage_chunks_of(j, nctas, nchunks):
+            lane, k = c % STAGE_LANES, c // STAGE_LANES
+            while world.flags.get(stage_flag(dst, src, "filled", lane), 0) < stage_count(seq, k + 1):
+                yield
+            got = world.ring[("stage", src, dst, lane, k % STAGE_SLOTS)]
+            assert got[:2] == (seq, c), f"staging slot holds chunk {got[:2]} where {(seq, c)} was expected"
+            got_chunks[c] = got[2]
+            world.flags[stage_flag(src, dst, "drained", lane)] = stage_count(seq, k + 1)
             yield
-        got = world.ring[("stage", src, dst, c % STAGE_SLOTS)]
-        assert got[:2] == (seq, c), f"staging slot holds chunk {got[:2]} where {(seq, c)} was expected"
-        source = got[2]
-        if c + 1 == nchunks and consumed is not None and CLEAR_CONSUMED_SLOTS:
-            world.flags[consumed] = 0
-        world.flags[drained] = stage_count(seq, c + 1)
-    world.mem[dst][op["local"]] = ("payload", src, source, n)
-    world.flags[lock] = 0
-MiB = 1 << 20
-CLEAR_CONSUMED_SLOTS = True   # what the device code does; the wrap test below also shows what happens without
+        done[0] += 1
+        if done[0] == nctas:
+            if consumed is not None and CLEAR_CONSUMED_SLOTS:
+                world.flags[consumed] = 0
+            assert sorted(got_chunks) == list(range(nchunks)) and len(set(got_chunks.values())) == 1
+            world.mem[dst][op["local"]] = ("payload", src, got_chunks[0], n)
+            world.flags[lock] = 0
+
+    yield from interleave(world, [cta(j) for j in range(nctas)])
 
 
 def plans_for(nranks, programs, options=None):
@@ -112,7 +144,8 @@ def window_local(word):
 
 
 class World:
-    def __init__(self, nranks):
+    def __init__(self, nranks, rng=None):
+        self.rng = rng or random.Random(0)
         self.flags = {}                                  # control words, job-wide addresses
         self.ring = {}                                   # eager slot address -> (seq, payload tag)
         self.mem = [dict() for _ in range(nranks)]       # per rank: buffer address -> payload tag
@@ -180,7 +213,7 @@ def role(world, rank, op):
 def simulate(nranks, plans, seed, on_group_done=None):
     """Each rank runs its groups in order (one stream); roles of the current groups interleave at random."""
     rng = random.Random(seed)
-    world = World(nranks)
+    world = World(nranks, rng)
     cursor = [0] * nranks
     live = [[] for _ in range(nranks)]
 
@@ -319,7 +352,7 @@ def test_unregistered_receive_buffers_go_through_the_staging_ring():
     keep = SEND_WIN, RECV_WIN
     try:
         SEND_WIN, RECV_WIN = 1 << 37, 1 << 38          # outside both windows
-        sizes = [600_000, 1 * MiB, 3 * MiB + 5, 4 * MiB, 9 * MiB, 33 * MiB + 1]
+        sizes = [600_000, 1 * MiB, 3 * MiB + 5, 4 * MiB, 9 * MiB, 33 * MiB + 1]   # 33 MiB: every lane wraps its slots
         check_phases(2, [[(0, 1, n)] for n in sizes] + [[(0, 1, n), (1, 0, n)] for n in sizes], seeds=(1, 2, 3))
         check_phases(3, [[(0, 1, 6 * MiB), (1, 2, 6 * MiB), (2, 0, 2 * MiB)]] * 3, seeds=(4, 5))
         # only the receiver unregistered: large messages are pulled as ever, mid-size ones are staged
