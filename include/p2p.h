@@ -136,6 +136,10 @@ P2P_API int p2p_register_export(void* buf, size_t bytes, void* blob);
 P2P_API int p2p_register_import(const void* all_blobs, int* window_id);
 /* Collective by convention: every rank drops the same window. */
 P2P_API int p2p_deregister(int window_id);
+/* Where `peer`'s part of a window is mapped in THIS process (NULL if that rank contributed nothing): for
+ * callers who run kernels or DMA copies of their own on peer memory.  No counterpart in the reference, which
+ * never sees a peer address (NCCL keeps its mappings to itself). */
+P2P_API int p2p_window_peer_ptr(int window_id, int peer, void** ptr);
 /* Convenience for bindings that cannot call cudaMalloc themselves (ctypes, cgo). */
 P2P_API int p2p_mem_alloc(void** ptr, size_t bytes);   /* nccl.h:130 ncclMemAlloc */
 P2P_API int p2p_mem_free(void* ptr);                   /* nccl.h:140 ncclMemFree */

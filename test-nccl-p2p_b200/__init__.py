@@ -32,7 +32,7 @@ PATH_AUTO, PATH_LDST, PATH_TMA, PATH_CE, PATH_EAGER, PATH_PULL = 0, 1, 2, 3, 4, 
 # every symbol include/p2p.h declares; tests check the library exports exactly these
 SYMBOLS = [
     "p2p_init", "p2p_blob_bytes", "p2p_export", "p2p_connect", "p2p_disconnect", "p2p_finalize", "p2p_rank", "p2p_nranks",
-    "p2p_register_blob_bytes", "p2p_register_export", "p2p_register_import", "p2p_deregister",
+    "p2p_register_blob_bytes", "p2p_register_export", "p2p_register_import", "p2p_deregister", "p2p_window_peer_ptr",
     "p2p_mem_alloc", "p2p_mem_free", "p2p_send", "p2p_recv", "p2p_group_start", "p2p_group_end", "p2p_alltoall",
     "p2p_symm_blob_bytes", "p2p_symm_alloc_export", "p2p_symm_alloc_import", "p2p_symm_free", "p2p_symm_multicast_ptr", "p2p_bcast",
     "p2p_get_error_string", "p2p_get_last_error", "p2p_get_async_error", "p2p_set_option", "p2p_get_option",
@@ -75,6 +75,7 @@ def lib() -> ctypes.CDLL:
         "p2p_register_export": (i32, [vp, sz, vp]),
         "p2p_register_import": (i32, [vp, ctypes.POINTER(i32)]),
         "p2p_deregister": (i32, [i32]),
+        "p2p_window_peer_ptr": (i32, [i32, i32, ctypes.POINTER(vp)]),
         "p2p_mem_alloc": (i32, [ctypes.POINTER(vp), sz]),
         "p2p_mem_free": (i32, [vp]),
         "p2p_send": (i32, [vp, sz, i32, i32, vp]),
@@ -193,6 +194,13 @@ def register(ptr: int, nbytes: int, allgather: Allgather = _single) -> int:
     win = ctypes.c_int(-1)
     check(L.p2p_register_import(joined, ctypes.byref(win)))
     return win.value
+
+
+def window_peer_ptr(window: int, peer: int) -> int:
+    """Address at which `peer`'s part of the window is mapped in this process (0: that rank contributed nothing)."""
+    p = ctypes.c_void_p()
+    check(lib().p2p_window_peer_ptr(window, peer, ctypes.byref(p)))
+    return p.value or 0
 
 
 def deregister(window: int) -> None:

@@ -74,7 +74,7 @@ struct alignas(8) OpDesc {
 // is served by one CTA on each side, so no chunk needs a barrier between CTAs: the lanes stream independently.
 // Counters are (seq << 24 | chunks of this lane), so they never need resetting.  One such message per ordered pair
 // at a time (`lock`, taken by the receiver before it asks).
-constexpr int kStageLanes = 16;
+constexpr int kStageLanes = 32;
 constexpr int kStageSlots = 4;
 struct StageHeader {                  // first 4 KiB of the ring area [region of rank r][from rank q]
     uint64_t filled[kStageLanes];     // q -> r traffic: chunks q has stored into each lane   (written by q)
@@ -242,20 +242,35 @@ __device__ __forceinline__ bool spin_flag(const uint64_t* flag, uint64_t timeout
 // each warp owns 32*UNROLL consecutive vectors and walks them in UNROLL coalesced steps of
 // 32 vectors, so the per-step offsets are immediates and one address register pair serves
 // all loads and one all stores.
+// `wait_hdr` (may be null): a pull may LOAD its first tile from the sender's buffer — which the sender has declared
+// ready — while the kernel ahead of this one on the stream is still retiring; only its STORES, into this rank's
+// buffer, have to wait for that kernel (griddepcontrol.wait).  The first tile's loads are therefore issued before
+// the wait: NVLink's ramp-up and the launch gap disappear behind the predecessor's tail.
 template <typename V, int UNROLL, typename LD, typename ST>
 __device__ __forceinline__ void copy_vectors(V* __restrict__ dst, const V* __restrict__ src,
-                                             size_t nvec, uint32_t part, uint32_t nparts, LD ld, ST st) {
+                                             size_t nvec, uint32_t part, uint32_t nparts, LD ld, ST st,
+                                             const GroupHdr* wait_hdr = nullptr) {
     const size_t tile = (size_t)blockDim.x * UNROLL;
     const size_t ntiles = nvec / tile;
     const size_t in_tile = (size_t)(threadIdx.x >> 5) * (32 * UNROLL) + (threadIdx.x & 31);
-    for (size_t t = part; t < ntiles; t += nparts) {
+    V v[UNROLL];
+    size_t t = part;
+    if (t < ntiles) {
         const V* s = src + t * tile + in_tile;
-        V* d = dst + t * tile + in_tile;
-        V v[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) v[u] = ld(s + u * 32);
+    }
+    if (wait_hdr) pdl_wait(*wait_hdr);
+    while (t < ntiles) {
+        V* d = dst + t * tile + in_tile;
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) st(d + u * 32, v[u]);
+        t += nparts;
+        if (t < ntiles) {
+            const V* s = src + t * tile + in_tile;
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) v[u] = ld(s + u * 32);
+        }
     }
     if (part == (uint32_t)(ntiles % nparts)) {
         for (size_t i = ntiles * tile + threadIdx.x; i < nvec; i += blockDim.x) st(dst + i, ld(src + i));
@@ -277,25 +292,31 @@ struct St16 { __device__ __forceinline__ void operator()(uint4* p, const uint4& 
 
 // Byte-exact copy of n bytes for arbitrary alignment of either side.  Each kernel
 // inlines it exactly once (see resolve_role), which keeps the hot loop free of spills.
+// With `wait_hdr` nothing is stored before pdl_wait (see copy_vectors).
 __device__ __forceinline__ void copy_bytes(uint8_t* dst, const uint8_t* src, size_t n, uint32_t part,
-                                           uint32_t nparts) {
-    if (n == 0) return;
+                                           uint32_t nparts, const GroupHdr* wait_hdr = nullptr) {
+    if (n == 0) {
+        if (wait_hdr) pdl_wait(*wait_hdr);
+        return;
+    }
     const uint64_t rel = ((uint64_t)dst ^ (uint64_t)src);
     if ((rel & 15) == 0) {
-        // same phase: byte head up to a 16-byte boundary, 16-byte body, byte tail
+        // same phase: 16-byte body first (its first loads may run ahead of the wait), then the byte head up to a
+        // 16-byte boundary and the byte tail
         size_t head = (16 - ((uint64_t)dst & 15)) & 15;
         if (head > n) head = n;
-        if (part == 0)
-            for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = __ldcv(src + i);
         uint8_t* d = dst + head;
         const uint8_t* s = src + head;
         const size_t left = n - head;
         const size_t body = left & ~(size_t)15;
-        copy_vectors<uint4, 8>((uint4*)d, (const uint4*)s, body / 16, part, nparts, Ld16{}, St16{});
+        copy_vectors<uint4, 8>((uint4*)d, (const uint4*)s, body / 16, part, nparts, Ld16{}, St16{}, wait_hdr);
+        if (part == 0)
+            for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = __ldcv(src + i);
         if (part == nparts - 1)
             for (size_t i = body + threadIdx.x; i < left; i += blockDim.x) d[i] = __ldcv(s + i);
         return;
     }
+    if (wait_hdr) pdl_wait(*wait_hdr);
     // different phase: widest element both sides can be aligned to at once
     const uint32_t w = (rel & 7) == 0 ? 8 : (rel & 3) == 0 ? 4 : (rel & 1) == 0 ? 2 : 1;
     size_t head = (w - ((uint64_t)dst & (w - 1))) & (w - 1);
@@ -396,10 +417,13 @@ __device__ __forceinline__ const uint8_t* recv_adaptive(const GroupHdr& h, const
         *smem_slot = v;
     }
     __syncthreads();
-    pdl_wait(h);  // only flags so far; from here on this rank's buffer is written (or offered to the sender)
     const uint64_t v = *smem_slot;
-    if (v == 0) return nullptr;
     const uint32_t win = (uint32_t)(v >> 40) & 0xffu;
+    // Only flags so far.  A pull goes on without waiting for the kernel ahead on this stream: its first loads (from
+    // the SENDER's buffer, declared ready by the word just read) may run ahead, its stores wait inside the copy
+    // loop.  Every other outcome writes or offers this rank's buffer from here on: wait now.
+    if (v == 0 || win == kWinPushPlease) pdl_wait(h);
+    if (v == 0) return nullptr;
     if (win == kWinPushPlease) {
         if (!op.word) return (const uint8_t*)kStagedMarker;  // neither buffer is in a window: the staging ring
         if (threadIdx.x == 0) {
@@ -412,6 +436,7 @@ __device__ __forceinline__ const uint8_t* recv_adaptive(const GroupHdr& h, const
     }
     const uint64_t base = ((const uint64_t*)op.aux)[win];
     if (!base) {
+        pdl_wait(h);
         if (threadIdx.x == 0) report_error(h, AERR_BAD_WINDOW);
         return nullptr;
     }
@@ -567,6 +592,7 @@ struct CopyJob {
     uint32_t staged;     // 0 direct, 1 sending through the staging ring, 2 receiving through it
     uint32_t chunk;      // staged: index of the chunk this pass moves (== nchunks: this CTA has none left)
     uint32_t nchunks;
+    const GroupHdr* wait_hdr;  // set: griddepcontrol.wait is still owed and happens inside the copy loop (pulls)
 };
 
 // Which chunks a CTA of a staged message serves: lane l belongs to CTA l % nblocks (on either side, whatever the
@@ -665,6 +691,7 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
     job.staged = 0;
     job.chunk = 0;
     job.nchunks = 0;
+    job.wait_hdr = nullptr;
     switch (op->kind) {
         case OP_PUSH:
             job.dst = push_wait_post(h, *op, part, slot);
@@ -686,6 +713,7 @@ __device__ __forceinline__ bool resolve_role(const GroupHdr& h, const OpDesc* op
             job.signal = op->f_signal2;
             job.consumed = op->f_wait2;
             if ((uint64_t)job.src == kStagedMarker) { stage_ask(h, *op, part); job.staged = 2; job.signal = 0; }
+            else if (job.src) job.wait_hdr = &h;   // a pull: see recv_adaptive
             return job.src != nullptr;
         case OP_RECV_STAGED:
             stage_ask(h, *op, part);

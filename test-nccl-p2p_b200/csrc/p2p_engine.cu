@@ -134,8 +134,10 @@ struct Options {
                                    // it loses to the pull kernel (256 MiB: 708 vs 726 GB/s streamed, 496 vs 368 us per
                                    // ping-pong hop): kernel -> DMA -> kernel on one stream costs more than the DMA gains.
     long long ce_wait_us = 200;    // how long p2p_send's host side waits for that word before using the SM path
-    long long stage_chunk = 256 << 10;  // bytes per slot of the staging ring's lanes (receive buffers that are in no window): 16 lanes
-                                        // x 4 slots x this per ordered pair of ranks; same on all ranks
+    long long stage_chunk = 0;     // bytes per slot of the staging ring's lanes (receive buffers that are in no window): 32 lanes x
+                                   // 4 slots x this per ordered pair of ranks; same on all ranks.  0: 256 KiB up to 8 ranks, less
+                                   // beyond, so that a rank's rings stay within 256 MiB (one lane moves ~18 GB/s whatever the
+                                   // chunk: 16 lanes 292 GB/s, 8 lanes 157; 128 KiB chunks 188 GB/s, 512 KiB 411)
     long long stage_lanes = kStageLanes;
     long long ce_flags = 1;        // who handles the flags around the DMA: 0 two one-thread kernels (round 1), 1 stream memory
                                    // operations (cuStreamWaitValue64 / cuStreamWriteValue64: nothing to launch, so the chain
@@ -309,7 +311,7 @@ const OptionSpec kOptionSpecs[] = {
     {"ce_min_bytes", "P2P_CE_MIN_BYTES", &Options::ce_min_bytes, -1, 1ll << 40},
     {"ce_wait_us", "P2P_CE_WAIT_US", &Options::ce_wait_us, 0, 10000000},
     {"ce_flags", "P2P_CE_FLAGS", &Options::ce_flags, 0, 2},
-    {"stage_chunk", "P2P_STAGE_CHUNK", &Options::stage_chunk, 4096, 16 << 20},
+    {"stage_chunk", "P2P_STAGE_CHUNK", &Options::stage_chunk, 0, 16 << 20},
     {"stage_lanes", "P2P_STAGE_LANES", &Options::stage_lanes, 1, kStageLanes},
 };
 
@@ -334,6 +336,17 @@ int validate_option(const OptionSpec& sp, long long value, const Options& o, con
     if (t.tma_peer_chunk * t.tma_peer_stages > 200 * 1024)
         return fail(P2P_INVALID_ARGUMENT, "%stma ring %lld x %lld bytes exceeds 200 KiB of shared memory", source, t.tma_peer_stages, t.tma_peer_chunk);
     return P2P_SUCCESS;
+}
+
+// The staging ring's chunk when left to the engine: a function of the rank count alone, so that all ranks agree.
+void resolve_stage_chunk(Options& o, int nranks) {
+    if (o.stage_chunk > 0) {
+        o.stage_chunk = std::max<long long>(4096, o.stage_chunk & ~255ll);
+        return;
+    }
+    long long chunk = 256 << 10;
+    while (chunk > (64 << 10) && chunk * kStageLanes * kStageSlots * nranks > (256ll << 20)) chunk >>= 1;
+    o.stage_chunk = chunk;
 }
 
 // Options from the environment, through the same checks as p2p_set_option.
@@ -1197,6 +1210,7 @@ int p2p_init(int rank, int nranks, int device) {
         if (rc) return rc;
     }
 
+    resolve_stage_chunk(o, nranks);
     // control region: per-peer flag sections, then the eager rings
     g.ll_slot_bytes = (size_t)std::max<long long>(o.eager_bytes, 8) * 2;
     g.ll_slot_bytes = (g.ll_slot_bytes + 255) & ~(size_t)255;
@@ -1535,6 +1549,18 @@ int p2p_deregister(int window_id) {
     return P2P_SUCCESS;
 }
 
+int p2p_window_peer_ptr(int window_id, int peer, void** ptr) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    int rc = check_ready();
+    if (rc) return rc;
+    if (!ptr) return fail(P2P_INVALID_ARGUMENT, "null argument");
+    if (window_id < 0 || window_id >= P2P_MAX_WINDOWS || !g.windows[window_id].used)
+        return fail(P2P_INVALID_ARGUMENT, "window %d is not registered", window_id);
+    if (peer < 0 || peer >= g.nranks) return fail(P2P_INVALID_ARGUMENT, "peer %d out of range [0,%d)", peer, g.nranks);
+    *ptr = g.windows[window_id].peer_base[peer];
+    return P2P_SUCCESS;
+}
+
 int p2p_mem_alloc(void** ptr, size_t bytes) {
     if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
     if (!ptr) return fail(P2P_INVALID_ARGUMENT, "null ptr");
@@ -1749,6 +1775,7 @@ int p2p_debug_plan_init(int rank, int nranks, int sm_count, int ctas_ldst, int c
         int rc = read_env_options(o);
         if (rc) return rc;
     }
+    resolve_stage_chunk(o, nranks);
     // the same layout arithmetic as p2p_init, over made-up base addresses: rank r's control region "lives" at
     // P2P_DEBUG_CTL_BASE + r * P2P_DEBUG_CTL_STRIDE, so tests can tell whose memory a flag address points into
     g.ll_slot_bytes = ((size_t)std::max<long long>(o.eager_bytes, 8) * 2 + 255) & ~(size_t)255;

@@ -19,7 +19,7 @@ p2p_group_kernel_ldst(const __grid_constant__ GroupArgsT<MAXOPS> a) {
     for (;;) {  // one pass - or, for a message that goes through the staging ring, one per chunk of this CTA's lanes
         const bool idle = job.staged && job.chunk >= job.nchunks;   // more CTAs than lanes, or a short message
         if (job.staged && !idle && !stage_begin(a.h, job, &slot)) return;
-        if (!idle) copy_bytes(job.dst, job.src, job.nbytes, job.staged ? 0 : job.part, job.staged ? 1 : job.op->nblocks);
+        if (!idle) copy_bytes(job.dst, job.src, job.nbytes, job.staged ? 0 : job.part, job.staged ? 1 : job.op->nblocks, job.wait_hdr);
         if (!job.staged || !stage_end(a.h, job)) break;
     }
     if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);
@@ -49,9 +49,9 @@ p2p_group_kernel_tma(const __grid_constant__ GroupArgs a) {
         const bool idle = job.staged && job.chunk >= job.nchunks;
         if (job.staged && !idle && !stage_begin(a.h, job, &slot)) return;
         if (!job.staged && (((uint64_t)job.dst ^ (uint64_t)job.src) & 15) == 0)
-            tma_push(job.dst, job.src, job.nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty);
+            tma_push(job.dst, job.src, job.nbytes, job.part, job.op->nblocks, a.h.tma_chunk, a.h.tma_stages, smem_ring, full, empty, job.wait_hdr);
         else if (!idle)
-            copy_bytes(job.dst, job.src, job.nbytes, job.staged ? 0 : job.part, job.staged ? 1 : job.op->nblocks);
+            copy_bytes(job.dst, job.src, job.nbytes, job.staged ? 0 : job.part, job.staged ? 1 : job.op->nblocks, job.wait_hdr);
         if (!job.staged || !stage_end(a.h, job)) break;
     }
     if (job.signal) movers_signal(a.h, *job.op, job.signal, job.consumed);

@@ -58,17 +58,26 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 
 // Push `n` bytes src -> dst with this CTA as `part` of `nparts`.  dst/src share their
 // 16-byte phase (checked by the caller); head and tail bytes go through the LSU.
+// `wait_hdr` (may be null; pulls): griddepcontrol.wait is still owed.  The producer's bulk LOADS from the sender's
+// buffer start at once and fill the ring while the kernel ahead on this stream retires; whatever STORES into this
+// rank's buffer - the consumer, the byte head and tail - waits first.
 __device__ __forceinline__ void tma_push(uint8_t* dst, const uint8_t* src, size_t n, uint32_t part,
                                          uint32_t nparts, uint32_t chunk, uint32_t stages,
-                                         uint8_t* smem_ring, uint64_t* full, uint64_t* empty) {
+                                         uint8_t* smem_ring, uint64_t* full, uint64_t* empty,
+                                         const GroupHdr* wait_hdr = nullptr) {
     size_t head = (16 - ((uint64_t)dst & 15)) & 15;
     if (head > n) head = n;
     const size_t body = (n - head) & ~(size_t)15;
     const size_t tail = n - head - body;
-    if (part == 0)
-        for (size_t i = threadIdx.x; i < head; i += blockDim.x) dst[i] = src[i];
-    if (part == nparts - 1)
-        for (size_t i = threadIdx.x; i < tail; i += blockDim.x) dst[head + body + i] = src[head + body + i];
+    if (wait_hdr && threadIdx.x != 0) pdl_wait(*wait_hdr);   // the producer (thread 0) waits after its loop
+    // byte head and tail: the upper half of the CTA, which drives nothing (the producer must not store before the wait)
+    if (threadIdx.x >= 64) {
+        const size_t lane = threadIdx.x - 64, step = blockDim.x - 64;
+        if (part == 0)
+            for (size_t i = lane; i < head; i += step) dst[i] = __ldcv(src + i);
+        if (part == nparts - 1)
+            for (size_t i = lane; i < tail; i += step) dst[head + body + i] = __ldcv(src + head + body + i);
+    }
 
     const uint8_t* s = src + head;
     uint8_t* d = dst + head;
@@ -89,6 +98,7 @@ __device__ __forceinline__ void tma_push(uint8_t* dst, const uint8_t* src, size_
             mbar_arrive_expect_tx(&full[st], bytes);
             bulk_g2s(smem_ring + (size_t)st * chunk, s + off, bytes, &full[st]);
         }
+        if (wait_hdr) pdl_wait(*wait_hdr);
     } else if (threadIdx.x == 32) {  // consumer
         for (size_t k = 0; k < mine; ++k) {
             const uint32_t st = (uint32_t)(k % stages);

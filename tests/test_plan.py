@@ -142,8 +142,8 @@ def test_receive_into_an_unregistered_buffer_goes_through_the_staging_ring():
     CTAs of its own and asks for the staging ring instead of posting a window."""
     res = plan(1, 2, [[["recv", LOOSE, 2 * MiB, 0]], [["recv", RECV_WIN, 2 * MiB, 0]], [["recv", LOOSE, 1000, 0]]])
     staged = res[0]["ops"][0]
-    assert res[0]["rc"] == 0 and staged["kind"] == "recv_staged" and staged["seq"] == 1 and staged["nblocks"] == 16
-    assert staged["signal_owner"] == 0 and res[0]["n_ctrl"] == 0 and res[0]["grid"] == 16
+    assert res[0]["rc"] == 0 and staged["kind"] == "recv_staged" and staged["seq"] == 1 and staged["nblocks"] == 32
+    assert staged["signal_owner"] == 0 and res[0]["n_ctrl"] == 0 and res[0]["grid"] == 32
     assert res[1]["rc"] == 0 and res[1]["ops"][0]["kind"] == "post" and res[1]["ops"][0]["seq"] == 2
     assert res[2]["rc"] == 0 and res[2]["ops"][0]["kind"] == "recv_ll"
     # a large message with neither buffer registered: the sender announces a push, the adaptive receive has no
@@ -257,7 +257,7 @@ def blob(rank, host_hash=hh.value, eager=p2p.get_option("eager_bytes"), pull=p2p
     head = struct.pack("<IIiiQiiQqQ", magic, 1, rank, nranks, host_hash, 424242 + rank, rank, eager, pull, cb.value)
     head += (bus if bus is not None else ("0000:%%02x:00.0" %% (rank + 1))).encode().ljust(32, b"\0")
     head += bytes(48 + 64)                                   # hostbox_name, ctl_handle
-    head += struct.pack("<II", stage_chunk, 16)              # stage_chunk, stage_lanes
+    head += struct.pack("<II", stage_chunk, 32)              # stage_chunk, stage_lanes
     return head + bytes(n - len(head))
 
 def connect(b0, b1):

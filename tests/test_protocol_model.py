@@ -31,7 +31,7 @@ WINDOWS = [[SEND_WIN, 1 << 30], [RECV_WIN, 4 << 30]]
 VALID, OFFMASK, PUSH_PLEASE, STAGED = 1 << 39, (1 << 39) - 1, 0xFF, 0xFE
 CTL_BASE, CTL_STRIDE = 0x100000000000, 0x1000000000
 SECTION = (64 * 4 + 4 + 8) * 8            # sizeof(PeerCtl)
-STAGE_CHUNK, STAGE_SLOTS, STAGE_LANES = 256 << 10, 4, 16
+STAGE_CHUNK, STAGE_SLOTS, STAGE_LANES = 256 << 10, 4, 32
 MiB = 1 << 20
 CLEAR_CONSUMED_SLOTS = True   # what the device code does; the wrap test below also shows what happens without
 
