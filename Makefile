@@ -105,7 +105,7 @@ clean:
 .PHONY: all oracle tests sass clean mpirun-link experiments
 
 # experiments and profiling harnesses (not part of the product; see scripts/README.md)
-experiments: $(BUILD)/exp_probe $(BUILD)/exp_peer_bw $(BUILD)/prof_peer
+experiments: $(BUILD)/exp_probe $(BUILD)/exp_peer_bw $(BUILD)/prof_peer $(BUILD)/exp_ce_chain
 $(BUILD)/exp_probe: scripts/exp_probe.cu
 	@mkdir -p $(BUILD)
 	$(NVCC) $(ARCH) -std=c++17 -O3 -o $@ $< -L$(CUDA_HOME)/lib64/stubs -lcuda
@@ -115,3 +115,6 @@ $(BUILD)/exp_peer_bw: scripts/exp_peer_bw.cu
 $(BUILD)/prof_peer: scripts/prof_peer.cu $(BUILD)/libb200p2p.a $(ENGINE_HDRS)
 	@mkdir -p $(BUILD)
 	$(NVCC) $(ARCH) -std=c++17 -O3 -lineinfo -Iinclude -I$(CSRC) -o $@ $< $(BUILD)/libb200p2p.a
+$(BUILD)/exp_ce_chain: scripts/exp_ce_chain.cu $(BUILD)/libb200p2p.a $(MPI_DEP)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(ARCH) -std=c++17 -O3 --extended-lambda -Iinclude $(MPI_INC) -o $@ $< $(BUILD)/libb200p2p.a $(MPI_LIB) -L$(CUDA_HOME)/lib64/stubs -lcuda

@@ -18,13 +18,15 @@
  *     <allgather the blobs in rank order>
  *     p2p_connect(all_blobs);
  *
- * Payload crosses NVLink exactly once, straight between the two user buffers, through a peer
- * mapping of a registered window (p2p_register_export / p2p_register_import, same two-phase
- * shape): messages up to the eager limit need no window; above it the sender's kernel stores
- * into the receiver's registered buffer (push); from the pull threshold up the receiver's
- * kernel loads from the sender's registered buffer instead when it is registered (pull, the
- * faster direction on B200), else the sender pushes.  Registering both buffers gives the
- * engine the choice; at least the receive buffer must be registered below the pull threshold.
+ * Buffers.  The reference passes plain cudaMalloc memory and registers nothing (p2p_matrix.cc:127-128), and so may
+ * a caller of this library: messages up to the eager limit travel through a ring in the engine's own memory, larger
+ * ones through a staging ring there when the receive buffer is in no window (chunk by chunk, copied out by the
+ * receiver: NCCL-like rates).  The fast path is one collective call per buffer, p2p_register_export /
+ * p2p_register_import (same two-phase shape as bootstrap): payload then crosses NVLink exactly once, straight between
+ * the two user buffers, through a peer mapping of the window.  Above the eager limit the sender's kernel stores into
+ * the receiver's registered buffer (push); from the pull threshold up the receiver's kernel loads from the sender's
+ * registered buffer instead when it is registered (pull, the faster direction on B200), else the sender pushes.
+ * Registering both buffers gives the engine the choice.
  *
  * Matching rules are NCCL's (nccl.h:438-462): the k-th p2p_send(count, dtype, peer=B) on
  * rank A pairs with the k-th p2p_recv(count, dtype, peer=A) on rank B, byte counts must
@@ -32,11 +34,20 @@
  * that must make progress together (bidirectional exchange, self-send) belong in one
  * p2p_group_start()/p2p_group_end() pair.
  *
- * Limits.  At most P2P_MAX_RANKS ranks, P2P_MAX_WINDOWS windows per rank, P2P_MAX_GROUP_OPS
- * operations per group, messages below 512 GiB, and at most 64 rendezvous-sized (4 eager-sized)
- * messages in flight per ordered pair of ranks — more than any one stream can have outstanding,
- * since each receive holds its stream until its payload has landed.  One host thread at a time.
- * Calls are not capturable into CUDA graphs (sequence numbers are assigned when a call is made).
+ * Limits.  At most P2P_MAX_RANKS ranks, one rank per GPU, P2P_MAX_WINDOWS windows per rank,
+ * P2P_MAX_GROUP_OPS operations per group, messages below 512 GiB.  Flag rings hold 64 rendezvous-sized
+ * (4 eager-sized) messages per ordered pair of ranks: message k+64 (k+4) between two ranks must not be
+ * issued before message k has completed — more than any one stream can have outstanding, since each
+ * receive holds its stream until its payload has landed — and one message at a time per ordered pair may
+ * go through the staging ring (a second one waits for the first).  One host thread at a time.  Calls are
+ * not capturable into CUDA graphs (sequence numbers are assigned when a call is made).
+ *
+ * Launch overlap.  Kernels of large messages are launched with programmatic stream serialisation, and a
+ * send whose payload the engine's own kernel ahead of it on the stream cannot be writing is announced to
+ * the receiver before that kernel has retired ("early post").  The check covers engine launches only: a
+ * kernel of the caller's that itself triggers programmatic launch completion early and then goes on to
+ * write the buffer of the next p2p_send on that stream is outside it — set P2P_EARLY_POST=0 (or
+ * P2P_PDL=1) in a program that does that.
  */
 #ifndef B200_P2P_H
 #define B200_P2P_H
@@ -198,18 +209,28 @@ P2P_API const char* p2p_get_last_error(void);
 /* Non-blocking: P2P_SUCCESS, or the first error a device kernel reported (peer timeout). */
 P2P_API int p2p_get_async_error(int* result);
 
-/* ---- tuning knobs (the reference has none; NCCL reads NCCL_* environment variables).
- *      Names: "path" (0 auto, 1 push with ld/st, 2 push with TMA), "nblocks" (CTAs per push, 0 auto),
- *      "pull_nblocks", "self_nblocks", "eager_bytes" and "pull_min_bytes" (protocol limits; must match
- *      on all ranks: environment only, read in p2p_init), "timeout_ms" (device spin timeout),
- *      "tma_chunk", "tma_stages", "tma_min_bytes", "pdl" (programmatic dependent launch),
- *      "loopback" (send-to-self goes through the wire protocol; for tests).  Environment:
- *      P2P_PATH, P2P_NBLOCKS, P2P_PULL_NBLOCKS, P2P_SELF_NBLOCKS, P2P_EAGER_BYTES, P2P_PULL_MIN_BYTES,
- *      P2P_TIMEOUT_MS, P2P_TMA_CHUNK, P2P_TMA_STAGES, P2P_TMA_MIN_BYTES, P2P_PDL, P2P_LOOPBACK,
- *      P2P_BIDIR_PUSH, P2P_SELF_TMA_MIN_BYTES, and the experimental copy-engine path
- *      P2P_CE_MIN_BYTES / P2P_CE_WAIT_US (off by default: measured slower than the pull kernel).
- *      p2p_get_option also answers "sm_count", "ctas_per_sm_ldst", "ctas_per_sm_tma",
- *      "stat_launches" (kernels launched so far) and "stat_ce_copies". ---- */
+/* ---- tuning knobs (the reference has none; NCCL reads NCCL_* environment variables).  Every option has an
+ *      environment variable P2P_<NAME> read (and range-checked) in p2p_init; p2p_set_option changes it afterwards
+ *      unless noted.  Protocol limits and ring shapes must be equal on all ranks (checked in p2p_connect) and
+ *      are environment-only: eager_bytes (may shrink later), pull_min_bytes, stage_chunk, stage_lanes.
+ *        path               0 auto, 1 push with ld/st, 2 push with TMA (P2P_PATH=auto|ldst|tma)
+ *        nblocks, pull_nblocks, self_nblocks, eager_nblocks     CTAs per push / pull / local copy / eager message, 0 auto
+ *        pull_total, push_total, fan_min     CTAs the flows of one group share, and the least each gets
+ *        bidir_push         a lone large send pushes when its group also receives a large message: 0 never,
+ *                           1 from that same peer (default), 2 from any peer, 3 also with several large sends
+ *        pull_tma_min_bytes a rank that pulls while being pulled from uses the TMA ring from this size (-1 never)
+ *        tma_chunk, tma_stages, tma_peer_chunk, tma_peer_stages, tma_min_bytes, self_tma_min_bytes     ring geometry, thresholds
+ *        pdl                programmatic dependent launch: 0 never, 1 eager-only and local-copy groups, 2 every
+ *                           group (trigger at kernel entry), 3 (default) as 1 plus groups of large messages
+ *        early_post         see "Launch overlap" above (default 1)
+ *        timeout_ms         device spin timeout (default 20000)
+ *        loopback           send-to-self goes through the wire protocol (tests)
+ *        ce_min_bytes, ce_wait_us, ce_flags     the experimental copy-engine path (off: measured slower)
+ *      p2p_get_option also answers "sm_count", "ctas_per_sm_ldst", "ctas_per_sm_tma", "stat_launches" (kernels
+ *      launched so far), "stat_ce_copies", and what the last launched group looked like: "stat_last_flavour"
+ *      (1 ld/st, 2 TMA), "stat_last_grid", "stat_last_block", "stat_last_push_ops", "stat_last_push_ctas",
+ *      "stat_last_offer_ops" (sends offered for pulling), "stat_last_recv_ops", "stat_last_recv_ctas",
+ *      "stat_last_eager_ops", "stat_last_copy_ctas", "stat_last_ce_ops", "stat_last_pdl". ---- */
 P2P_API int p2p_set_option(const char* name, long long value);
 P2P_API int p2p_get_option(const char* name, long long* value);
 /* What the selector would do for a message of `bytes` to `peer`: writes the path id
