@@ -384,8 +384,14 @@ def engine_arm(args):
     else:
         roof = {"bound": "nvlink", "achieved": round(B / per_step / 1e9, 2), "peak": LINK_GBPS, "unit": "GB/s",
                 "peak_kind": f"nominal NVLink 5 per direction per GPU; measured peer copy on this pool {LINK_MEASURED_GBPS}",
-                "traffic": TRAFFIC_PER_LAUNCH.get("peer")}
+                "traffic": None}
     roof["frac"] = round(roof["achieved"] / roof["peak"], 4)
+    if world > 1 and B == (256 << 20) and not ce_copies:
+        mover = "peer_push_ldst" if last["push_ops"] else ("peer_pull_tma" if last["flavour"] == 2 else "peer_pull_ldst")
+        roof["traffic"] = TRAFFIC_PER_LAUNCH[mover]
+        roof["traffic_from"] = ("profiles/r02_ncu/" + {"peer_push_ldst": "traffic_push_256M.csv", "peer_pull_ldst": "traffic_pull_256M.csv",
+                                                       "peer_pull_tma": "traffic_tmapull_256M.csv"}[mover]
+                                + " (ncu, single-process two-GPU launch of this mover)")
     if world > 1:
         roof["frac_measured"] = round(roof["achieved"] / LINK_MEASURED_GBPS, 4)
         roof["peak_measured"] = LINK_MEASURED_GBPS
@@ -451,10 +457,16 @@ def engine_arm(args):
     return 0
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel, from the committed ncu --set full
-# capture of this same command at N=1 (profiles/r01_ncu/prof_local_tma.raw.csv: 268.49 MB read + 212.76 MB written,
-# the rest of the 268 MB written still sits in L2 when the kernel ends).  No ncu on multi-rank runs: null there.
-TRAFFIC_PER_LAUNCH = {"local": 481247232, "peer": None}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel's mover, from committed ncu captures at the
+# bench's 256 MiB message size.
+#   local:      profiles/r01_ncu/prof_local_tma.raw.csv, this same command at N=1: 268.49 MB read + 212.76 MB written (the
+#               rest of the 268 MB written still sits in L2 when the kernel ends).
+#   peer_*:     profiles/r02_ncu/traffic_*_256M.csv: the engine's group kernels launched with peer pointers by ONE process
+#               that drives two GPUs (scripts/prof_peer.cu; ncu must not wrap a multi-rank command).  A push reads its
+#               payload from local DRAM (268.5 MB + 3.2 MB written); a pull writes it to local DRAM (208-209 MB, the rest
+#               in L2 at kernel end) and reads nothing locally.  In a ring step the same GPU's DRAM also serves the
+#               neighbour's pull (another 268 MB read), which belongs to the neighbour's launch.
+TRAFFIC_PER_LAUNCH = {"local": 481247232, "peer_push_ldst": 271659008, "peer_pull_ldst": 208919296, "peer_pull_tma": 207791616}
 
 
 def side_measurements(p2p, torch, rank, world, stream, src, dst, B, barrier, max_over_ranks, gather):

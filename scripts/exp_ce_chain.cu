@@ -48,11 +48,16 @@ int main(int argc, char** argv) {
     const int peer = 1 - rank;
     uint8_t *src, *dst;
     uint64_t* flags;  // [0] ready, [1] done, [2] release of the polling kernels
-    CK(cudaMalloc(&src, bytes)); CK(cudaMalloc(&dst, bytes)); CK(cudaMalloc(&flags, 4096));
+    const size_t slack = getenv("EXP_DST_SLACK") ? 256 : 0;   // the matrix driver's receive buffer is bytes + 256
+    CK(cudaMalloc(&src, bytes)); CK(cudaMalloc(&dst, bytes + slack)); CK(cudaMalloc(&flags, 4096));
     CK(cudaMemset(src, rank + 1, bytes)); CK(cudaMemset(flags, 0, 4096));
     CK(cudaDeviceSynchronize());
-    int wdst = -1, wflags = -1;
-    P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, dst, bytes, &wdst));
+    int wdst = -1, wflags = -1, wsrc = -1;
+    P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, dst, bytes + slack, &wdst));
+    if (getenv("EXP_REGISTER_SRC")) {   // is a DMA slower when its SOURCE is a cudaIpc-exported buffer a peer has mapped?
+        P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, src, bytes, &wsrc));
+        if (!rank) printf("(source buffer registered as a window too)\n");
+    }
     P2PCHECK(p2p_register_mpi(MPI_COMM_WORLD, flags, 4096, &wflags));
     void *pdst = nullptr, *pflags_v = nullptr;
     P2PCHECK(p2p_window_peer_ptr(wdst, peer, &pdst));
@@ -118,6 +123,71 @@ int main(int argc, char** argv) {
         CK(cudaMemcpyAsync(pdst, src, bytes, cudaMemcpyDefault, s));
         CU(cuStreamWriteValue64((CUstream)s, (CUdeviceptr)(pflags + 1), seq, 0));
     });
+    run("H  D with a local stream write between the wait and the DMA (the engine zeroes the consumed post slot there)", [&] {
+        ++seq;
+        CU(cuStreamWriteValue64((CUstream)s, (CUdeviceptr)(pflags + 0), seq, 0));
+        CU(cuStreamWaitValue64((CUstream)s, (CUdeviceptr)(flags + 0), seq, CU_STREAM_WAIT_VALUE_GEQ));
+        CU(cuStreamWriteValue64((CUstream)s, (CUdeviceptr)(flags + 8), seq, 0));
+        CK(cudaMemcpyAsync(pdst, src, bytes, cudaMemcpyDefault, s));
+        CU(cuStreamWriteValue64((CUstream)s, (CUdeviceptr)(pflags + 1), seq, 0));
+        CU(cuStreamWaitValue64((CUstream)s, (CUdeviceptr)(flags + 1), seq, CU_STREAM_WAIT_VALUE_GEQ));
+    });
+    // F: the engine's shape - the chain on a SIDE stream, forked from and joined to the main stream by events every step
+    // (the host enqueues many steps ahead, so each event wait sits in its queue for a whole step before it is satisfied)
+    {
+        cudaEvent_t fork, join;
+        CK(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&join, cudaEventDisableTiming));
+        run("F  D's chain on a side stream, forked/joined by events each step", [&] {
+            ++seq;
+            CK(cudaEventRecord(fork, s));
+            CK(cudaStreamWaitEvent(s2, fork, 0));
+            CU(cuStreamWriteValue64((CUstream)s2, (CUdeviceptr)(pflags + 0), seq, 0));
+            CU(cuStreamWaitValue64((CUstream)s2, (CUdeviceptr)(flags + 0), seq, CU_STREAM_WAIT_VALUE_GEQ));
+            CK(cudaMemcpyAsync(pdst, src, bytes, cudaMemcpyDefault, s2));
+            CU(cuStreamWriteValue64((CUstream)s2, (CUdeviceptr)(pflags + 1), seq, 0));
+            CU(cuStreamWaitValue64((CUstream)s2, (CUdeviceptr)(flags + 1), seq, CU_STREAM_WAIT_VALUE_GEQ));
+            CK(cudaEventRecord(join, s2));
+            CK(cudaStreamWaitEvent(s, join, 0));
+        });
+        run("F' as F, plus a 65-CTA polling kernel for 'done' on the main stream (engine: receive kernel beside the chain)", [&] {
+            ++seq;
+            CK(cudaEventRecord(fork, s));
+            CK(cudaStreamWaitEvent(s2, fork, 0));
+            poll_kernel<<<65, 512, 0, s>>>(flags + 1, seq, 2000000000ull);
+            CU(cuStreamWriteValue64((CUstream)s2, (CUdeviceptr)(pflags + 0), seq, 0));
+            CU(cuStreamWaitValue64((CUstream)s2, (CUdeviceptr)(flags + 0), seq, CU_STREAM_WAIT_VALUE_GEQ));
+            CK(cudaMemcpyAsync(pdst, src, bytes, cudaMemcpyDefault, s2));
+            CU(cuStreamWriteValue64((CUstream)s2, (CUdeviceptr)(pflags + 1), seq, 0));
+            CK(cudaEventRecord(join, s2));
+            CK(cudaStreamWaitEvent(s, join, 0));
+        });
+    }
+    // G: one way only.  Rank 1's stream memory wait for 'done' lasts a whole DMA: does a long wait react late?
+    {
+        const uint64_t base = seq;
+        for (int i = 0; i < 3 + iters; ++i) {
+            if (i == 3) { CK(cudaStreamSynchronize(s)); MPI_Barrier(MPI_COMM_WORLD); CK(cudaEventRecord(e0, s)); }
+            ++seq;
+            if (rank == 0) {
+                CU(cuStreamWaitValue64((CUstream)s, (CUdeviceptr)(flags + 0), seq, CU_STREAM_WAIT_VALUE_GEQ));
+                CK(cudaMemcpyAsync(pdst, src, bytes, cudaMemcpyDefault, s));
+                CU(cuStreamWriteValue64((CUstream)s, (CUdeviceptr)(pflags + 1), seq, 0));
+            } else {
+                CU(cuStreamWriteValue64((CUstream)s, (CUdeviceptr)(pflags + 0), seq, 0));
+                CU(cuStreamWaitValue64((CUstream)s, (CUdeviceptr)(flags + 1), seq, CU_STREAM_WAIT_VALUE_GEQ));
+            }
+        }
+        (void)base;
+        CK(cudaEventRecord(e1, s));
+        CK(cudaStreamSynchronize(s));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        double t = ms * 1e-3 / iters, tmax = 0;
+        MPI_Allreduce(&t, &tmax, 1, MPI_DOUBLE, MPI_MAX, MPI_COMM_WORLD);
+        if (!rank) printf("%-78s %8.1f us per step  %8.1f GB/s one way\n", "G  one way: receiver = memop ready + memop wait for done (a DMA long)", tmax * 1e6, bytes / tmax / 1e9);
+        MPI_Barrier(MPI_COMM_WORLD);
+    }
     // payload check
     uint8_t probe[2];
     CK(cudaMemcpy(probe, dst, 1, cudaMemcpyDefault)); CK(cudaMemcpy(probe + 1, dst + bytes - 1, 1, cudaMemcpyDefault));

@@ -6,6 +6,7 @@
 #include "p2p_internal.h"
 
 #include <algorithm>
+#include <array>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -180,6 +181,7 @@ struct Engine {
     cudaEvent_t ce_join[P2P_MAX_RANKS] = {};
     cudaEvent_t ce_fork = nullptr;
     long long stat_launches = 0, stat_ce_copies = 0;
+    std::vector<std::array<cudaEvent_t, 3>> ce_timing;  // P2P_CE_TIMING: chain start, DMA start, DMA end
     uint64_t* ce_vals = nullptr;                // pinned host ring of flag values for ce_flags 2 (source of the 8-byte DMAs)
     uint32_t ce_vals_next = 0;
     // what the last launched group looked like (bench.py reports the kernel that actually ran, not a forecast)
@@ -950,6 +952,13 @@ int submit_copy_engine_chain(const PendingOp& op, const Resolved& r, const Group
     uint64_t* done = &peer_section(theirs, me)->done[seq % kRing];
     cudaStream_t cs = g.ce_stream[p];
     CUDA_TRY(cudaStreamWaitEvent(cs, g.ce_fork, 0));
+    // P2P_CE_TIMING=1 (experiments): where a chain's time goes - events before the handshake, before and after the DMA
+    static const bool timing = getenv("P2P_CE_TIMING") != nullptr;
+    cudaEvent_t tev[3] = {};
+    if (timing && g.ce_timing.size() < 512) {
+        for (cudaEvent_t& e : tev) CUDA_TRY(cudaEventCreate(&e));
+        CUDA_TRY(cudaEventRecord(tev[0], cs));
+    }
     if (g.opt.ce_flags == 0) {
         CUDA_TRY(launch_ce_wait(notice, make_post_word(seq, kWinPushPlease, 0), post, seq, word, hdr, cs));
         CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
@@ -963,9 +972,12 @@ int submit_copy_engine_chain(const PendingOp& op, const Resolved& r, const Group
         if (wr != 0) return fail(P2P_UNHANDLED_CUDA_ERROR, "cuStreamWaitValue64 failed with CUresult %d", wr);
         rc = stream_write_flag(cs, post, 0, false);  // consumed (see movers_signal)
         if (rc) return rc;
+        if (tev[0]) CUDA_TRY(cudaEventRecord(tev[1], cs));
         CUDA_TRY(cudaMemcpyAsync(dst, op.buf, op.nbytes, cudaMemcpyDefault, cs));
+        if (tev[0]) CUDA_TRY(cudaEventRecord(tev[2], cs));
         rc = stream_write_flag(cs, done, seq, true);
         if (rc) return rc;
+        if (tev[0]) g.ce_timing.push_back({tev[0], tev[1], tev[2]});
     }
     CUDA_TRY(cudaEventRecord(g.ce_join[p], cs));
     CUDA_TRY(cudaStreamWaitEvent(launch_stream, g.ce_join[p], 0));
@@ -1408,6 +1420,23 @@ int p2p_finalize(void) {
         return P2P_SUCCESS;
     }
     disconnect_locked();  // a no-op when p2p_disconnect has run
+    if (!g.ce_timing.empty()) {
+        cudaDeviceSynchronize();
+        double hs = 0, dma = 0, gap = 0;
+        size_t n = 0, ngap = 0;
+        for (size_t i = g.ce_timing.size() / 4; i < g.ce_timing.size(); ++i) {  // skip the warm-up quarter
+            float a = 0, b = 0;
+            if (cudaEventElapsedTime(&a, g.ce_timing[i][0], g.ce_timing[i][1]) != cudaSuccess) continue;
+            if (cudaEventElapsedTime(&b, g.ce_timing[i][1], g.ce_timing[i][2]) != cudaSuccess) continue;
+            hs += a; dma += b; ++n;
+            float c = 0;
+            if (i + 1 < g.ce_timing.size() && cudaEventElapsedTime(&c, g.ce_timing[i][2], g.ce_timing[i + 1][0]) == cudaSuccess) { gap += c; ++ngap; }
+        }
+        if (n) printf("[rank %d] copy-engine chains: handshake %.1f us, DMA %.1f us, from DMA end to the next chain's start %.1f us (mean of %zu)\n",
+                      g.rank, hs / n * 1e3, dma / n * 1e3, ngap ? gap / ngap * 1e3 : 0.0, n);
+        for (auto& t : g.ce_timing) for (cudaEvent_t e : t) cudaEventDestroy(e);
+        g.ce_timing.clear();
+    }
     symm_finalize(g.nranks);
     for (int r = 0; r < P2P_MAX_RANKS; ++r) {
         g.peer_ctl[r] = nullptr;
@@ -1565,6 +1594,9 @@ int p2p_mem_alloc(void** ptr, size_t bytes) {
     if (!g.inited) return fail(P2P_INVALID_USAGE, "p2p_init has not been called");
     if (!ptr) return fail(P2P_INVALID_ARGUMENT, "null ptr");
     CUDA_TRY(cudaSetDevice(g.device));
+    // whole 2 MiB pages from 2 MiB up: an allocation of any other size gets a slower peer mapping (copy engine both
+    // ways into a 256 MiB + 256 B buffer: 1084 GB/s, into a 256 MiB one: 1521)
+    if (bytes >= (2u << 20)) bytes = (bytes + (2u << 20) - 1) & ~(size_t)((2u << 20) - 1);
     CUDA_TRY(cudaMalloc(ptr, bytes ? bytes : 1));
     return P2P_SUCCESS;
 }

@@ -74,6 +74,12 @@ struct EngineBackend {
     }
 
     void finalize() {
+        if (getenv("P2P_PRINT_STATS")) {  // experiments: how many kernels were launched, how many payloads went by DMA
+            long long launches = 0, ce = 0;
+            p2p_get_option("stat_launches", &launches);
+            p2p_get_option("stat_ce_copies", &ce);
+            printf("[rank %d] kernels launched %lld, payloads handed to the copy engine %lld\n", p2p_rank(), launches, ce);
+        }
         int aerr = 0;
         if (p2p_get_async_error(&aerr) == P2P_SUCCESS && aerr != P2P_SUCCESS) {
             printf("Failed, P2P async error '%s' (%s)\n", p2p_get_error_string(aerr), p2p_get_last_error());
