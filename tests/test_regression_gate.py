@@ -48,3 +48,35 @@ def test_latency_cells_are_lower_is_better(tmp_path):
     assert gate(str(e), str(tmp_path / "e.json"), "--quiet").returncode == 0
     (tmp_path / "empty.json").write_text("")
     assert gate(str(e), str(tmp_path / "empty.json")).returncode == 2
+
+
+R2 = os.path.join(ROOT, "profiles", "r02_raw")
+
+
+def test_round2_results_hold_against_nccl():
+    """Round 2's committed records: all-pairs on 8 GPUs (the round's shared CTA budget must not cost what round 1 had),
+    the uni-directional matrix on 8 GPUs above 82 % of the link on every pair, and BASELINE cfg 5 at FOUR ranks
+    (round 1 had the sweep at 2 and 8 only) - engine against NCCL from the same calls."""
+    n8, n4 = os.path.join(R2, "n8_run1"), os.path.join(R2, "n4_run1")
+    p = gate(os.path.join(n8, "cfg4_engine.json"), os.path.join(n8, "cfg4_nccl.json"), "--min-ratio", "1.05", "--quiet")
+    assert p.returncode == 0, p.stdout
+    recs = [json.loads(l) for l in open(os.path.join(n8, "cfg4_engine.json"))]
+    assert recs[0]["ranks"] == 8 and recs[0]["GBps"] >= 4820          # round 1's best all-pairs figure
+    uni = [json.loads(l) for l in open(os.path.join(n8, "cfg2_engine.json")) if '"mode": "uni"' in l]
+    assert len(uni) == 56 and min(r["GBps"] for r in uni) >= 0.82 * 900
+    p = gate(os.path.join(n4, "sweep_engine.json"), os.path.join(n4, "sweep_nccl.json"), "--quiet")
+    assert p.returncode == 0, p.stdout
+
+
+def test_round2_four_gpu_bench_line_guards_all_pairs_and_parity():
+    """The 4-GPU bench line of round 2 (bench.py on the box): all-pairs at 64 MiB per flow at or above what the code
+    gave before round 1's 8-GPU tuning starved it (2426 GB/s) and above NCCL from the same run; the ring step above
+    round 1's 597 GB/s per GPU; engine and NCCL digests equal in all 28 cells."""
+    line = [l for l in open(os.path.join(R2, "n4_run1", "bench_engine.log")) if l.startswith('{"metric"')][-1]
+    rec = json.loads(line)
+    ex = rec["extras"]
+    assert rec["n_gpus"] == 4 and ex["allpairs_bytes_per_flow"] == 64 << 20
+    assert ex["allpairs_aggregate_GBps"] >= 2426 and ex["allpairs_aggregate_GBps"] > 1.2 * ex["nccl_allpairs_aggregate_GBps"]
+    assert ex["latency_8B_oneway_us"] < ex["nccl_latency_8B_oneway_us"]
+    assert rec["roofline"]["achieved"] >= 630 and rec["value"] > 1.8 * rec["nccl_same_run"]["value"]
+    assert rec["parity"]["nccl_digests_equal"] is True and rec["parity"]["cells"] == 28 and rec["parity"]["mismatching_bytes"] == 0
