@@ -624,9 +624,17 @@ int resolve_protocols(const std::vector<PendingOp>& ops, const std::vector<int>&
             // exchange (one large send, and a large receive from that same peer in the group), where two pushes
             // interfere less than two pulls (1.32 vs 1.24 TB/s between two B200s).  With several large sends in
             // the group (fan-out, all-pairs) pulls with few CTAs win again (4.83 vs 4.28 TB/s on 8 GPUs).
-            bool from_same_peer = false;
-            for (size_t j = 0; j < ops.size(); ++j)
-                if (!ops[j].is_send && ops[j].peer == op.peer && partner[j] < 0 && is_large(ops[j].nbytes)) from_same_peer = true;
+            // A push needs the RECEIVER's buffer in a window.  What the peer registered is not known here, but in an
+            // exchange both ends usually treat their buffers alike: if this rank's own large receives of the group
+            // are in no window, a push would most likely end in the staging ring, where a pull goes straight.
+            bool from_same_peer = false, my_recvs_registered = true;
+            for (size_t j = 0; j < ops.size(); ++j) {
+                if (ops[j].is_send || partner[j] >= 0 || !is_large(ops[j].nbytes)) continue;
+                if (ops[j].peer == op.peer) from_same_peer = true;
+                uint32_t w;
+                uint64_t o;
+                if (!lookup_window(ops[j].buf, ops[j].nbytes, &w, &o)) my_recvs_registered = false;
+            }
             bool push_instead = false;
             switch (g.opt.bidir_push) {
                 case 1: push_instead = from_same_peer && shape.n_large_sends == 1; break;
@@ -634,6 +642,7 @@ int resolve_protocols(const std::vector<PendingOp>& ops, const std::vector<int>&
                 case 3: push_instead = shape.n_large_recvs > 0; break;
                 default: break;
             }
+            if (r.registered && !my_recvs_registered) push_instead = false;
             r.pull_send = r.registered && !push_instead && g.opt.path != 2 && g.opt.path != 1;
         }
         if (op.is_send && !(r.proto == PROTO_LARGE && r.pull_send) && push_flavour(op.nbytes) == 2) shape.flavour = FLAVOUR_TMA;

@@ -344,3 +344,18 @@ print("rc", rc, L.p2p_get_last_error().decode())
         assert out.startswith("rc 4 ") and word in out, (env, out)
     out = run([sys.executable, "-c", code], env={"CUDA_VISIBLE_DEVICES": "", "P2P_TMA_CHUNK": "16384", "P2P_PATH": "tma"}).stdout
     assert out.startswith("rc 0"), out
+
+
+def test_pairwise_exchange_pulls_when_only_the_send_buffers_are_windows():
+    """A pairwise exchange pushes both ways - unless this rank's own receive buffer is in no window: the peer's then
+    most likely is not either, a push would end in the staging ring, and a pull (which needs only the SEND buffer
+    registered) goes straight."""
+    n = 32 * MiB
+    (g,) = plan(0, 2, [[["send", SEND_WIN, n, 1], ["recv", RECV_WIN, n, 1]]])
+    assert sorted(kinds(g)) == ["push", "recv_adapt"]
+    (g,) = plan(0, 2, [[["send", SEND_WIN, n, 1], ["recv", LOOSE, n, 1]]])
+    assert sorted(kinds(g)) == ["post", "recv_adapt"]                      # the send is offered for pulling
+    adapt = next(o for o in g["ops"] if o["kind"] == "recv_adapt")
+    assert adapt["word"] == 0                                              # nothing to post: it pulls, or asks for the ring
+    (g,) = plan(0, 2, [[["send", LOOSE, n, 1], ["recv", LOOSE, n, 1]]])   # nothing registered at all: push into the ring
+    assert sorted(kinds(g)) == ["push", "recv_adapt"]

@@ -357,6 +357,6 @@ def test_unregistered_receive_buffers_go_through_the_staging_ring():
         check_phases(3, [[(0, 1, 6 * MiB), (1, 2, 6 * MiB), (2, 0, 2 * MiB)]] * 3, seeds=(4, 5))
         # only the receiver unregistered: large messages are pulled as ever, mid-size ones are staged
         SEND_WIN = keep[0]
-        check_phases(2, [[(0, 1, n)] for n in sizes], seeds=(6,))
+        check_phases(2, [[(0, 1, n)] for n in sizes] + [[(0, 1, n), (1, 0, n)] for n in sizes], seeds=(6, 7))
     finally:
         SEND_WIN, RECV_WIN = keep

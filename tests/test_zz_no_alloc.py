@@ -91,6 +91,25 @@ def test_exactly_the_largest_buffer_the_scratch_covers(engine):
     del buf
 
 
+def test_each_device_of_a_process_has_its_own_scratch(p2p, oracle):
+    """Two GPUs driven by one process (needs two; skipped otherwise): the scratch array exists once per device, and
+    the entry point looks up the current device's copy on its first call there."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    n = (3 << 20) + 5
+    data = ((np.arange(n, dtype=np.int64) * 40503) & 0xFF).astype(np.uint8)
+    want = oracle.digest(data)
+    for dev in (0, 1, 0):
+        torch.cuda.set_device(dev)
+        buf = torch.from_numpy(data).to(f"cuda:{dev}")
+        out = torch.zeros(1, dtype=torch.int64, device=f"cuda:{dev}")
+        p2p.digest_noalloc(buf.data_ptr(), n, out.data_ptr())
+        torch.cuda.synchronize(dev)
+        assert int(out.cpu().numpy().view(np.uint64)[0]) == want, dev
+    torch.cuda.set_device(0)
+
+
 def test_works_in_a_process_that_never_initialised_the_engine(p2p, oracle):
     """Fresh process, no p2p_init, no allocation by the library: the value still matches."""
     from conftest import ROOT, run
