@@ -750,6 +750,9 @@ void size_roles(const std::vector<PendingOp>& ops, std::vector<Resolved>& res, G
                     else { r.nblocks = mover_ctas(op.nbytes, shape.flavour, self, false, shape.n_large_sends, shape.tma_chunk); want += r.nblocks; }
                 } else {
                     r.nblocks = mover_ctas(op.nbytes, FLAVOUR_LDST, self, true, shape.n_large_recvs);
+                    // a lone pull through the bulk-copy ring (ring step) likes a few more, lighter CTAs: 96 of 128 threads
+                    // 646-648 GB/s per GPU on 4 and 8 B200s, 64: 639-640, 147: 641
+                    if (shape.flavour == FLAVOUR_TMA && shape.n_large_recvs == 1 && !g.opt.pull_nblocks && r.nblocks == 64) r.nblocks = 96;
                     want += r.nblocks;
                 }
                 break;
