@@ -241,7 +241,8 @@ def reference_arm(args):
         "dtype": "u8", "data": "synthetic",
         "config": {"workload": f"ring step, {args.size} bytes per GPU (BASELINE configs[1] message size)", "bytes": args.size,
                    "what": "reference's own path: ncclSend/ncclRecv from libnccl 2.27.3 in the reference's loop "
-                           "(oracle/_ref/p2p_matrix_nccl), launched by mpirun on the same GPUs",
+                           "(oracle/_ref/p2p_matrix_nccl), launched by mpirun on the same GPUs; plain cudaMalloc buffers, "
+                           "not registered with NCCL, default NCCL environment - as the reference runs it",
                    "l2": "message larger than L2 (126 MB)" if args.size > (126 << 20) else "message fits L2"},
         "e2e": {"value": round(e2e[0]["GBps"], 3) if e2e else None, "unit": "GB/s",
                 "h2d_bytes_per_step": args.size * n if e2e else 0, "d2h_bytes_per_step": args.size * n if e2e else 0,
@@ -445,7 +446,7 @@ def engine_arm(args):
             recs, log = nccl_run(world, "ring", B, min(K, 200), 5)
             ring = [r for r in (recs or []) if r["mode"] == "ring"]
             line["nccl_same_run"] = ({"value": round(ring[0]["GBps"], 3), "unit": "GB/s", "ms_per_step": round(ring[0]["seconds"] * 1e3, 6),
-                                      "what": "ncclSend/ncclRecv ring step, libnccl 2.27.3, device timing"} if ring
+                                      "what": "ncclSend/ncclRecv ring step, libnccl 2.27.3, unregistered buffers (the reference's way), device timing"} if ring
                                      else {"unavailable": str(log)[-200:]})
         print(json.dumps(line), flush=True)
     if world > 1:
