@@ -410,7 +410,9 @@ int p2p_symm_alloc_import(const void* all_blobs, void** ptr, int* window_id) {
         if (cr != CUDA_SUCCESS) return fail_out(set_last_error(P2P_UNHANDLED_CUDA_ERROR, "mapping rank %d's part of the window failed with CUresult %d", r, (int)cr));
     }
     // the multicast object: import, join with this device, bind this rank's part (the bind waits until every rank
-    // has joined), map.  Any failure here only loses the multicast path.
+    // has joined), map.  Whether there is a multicast path was decided by rank 0 at export time for all ranks alike; a
+    // rank that cannot join it fails its import, because a root that stores through the multicast mapping would
+    // never reach this rank's copy.
     if (blobs[0].has_mc) {
         CUresult cr = CUDA_SUCCESS;
         if (e.rank != 0) {
