@@ -131,3 +131,18 @@ def test_mpi_glue_fails_on_every_rank_without_hanging(built, n):
     out = run([MPIRUN, "-n", str(n), exe], timeout=60).stdout
     lines = [l for l in out.splitlines() if l.startswith("rank ")]
     assert len(lines) == n and all("init=1 (unhandled cuda error)" in l for l in lines), out
+
+
+def test_every_option_of_the_engine_is_documented_in_the_header():
+    """The option table in csrc/p2p_engine.cu (one entry per name, environment variable and range) against the list
+    of tuning knobs in include/p2p.h: an option a caller can set must be described where callers look."""
+    import re
+    src = open(os.path.join(ROOT, "test-nccl-p2p_b200", "csrc", "p2p_engine.cu")).read()
+    table = src[src.index("const OptionSpec kOptionSpecs[]"):]
+    table = table[:table.index("};")]
+    specs = re.findall(r'\{"(\w+)",\s*"(P2P_\w+)"', table)
+    assert len(specs) >= 25
+    header = open(os.path.join(ROOT, "include", "p2p.h")).read()
+    for name, env in specs:
+        assert env == "P2P_" + name.upper(), (name, env)
+        assert re.search(r"\b%s\b" % name, header), f"option '{name}' is missing from include/p2p.h"
